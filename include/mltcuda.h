@@ -26,6 +26,9 @@
 #ifdef __cplusplus
 extern "C" {
 #endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
 
 #define MLTCUDA_ABI_VERSION 1
 
@@ -236,9 +239,13 @@ enum {
 typedef struct mltcuda_tractor_op
 {
     int kind;
-    int to_format; /* MLTCUDA_TOP_CONVERT */
-    /* composite placement inside the A frame (pixels): dest rect origin after clipping */
-    int x, y;
+    int to_format; /* MLTCUDA_TOP_CONVERT: MLTCUDA_FMT_YUV422 or MLTCUDA_FMT_RGBA */
+    /* MLTCUDA_TOP_COMPOSITE: fill u.composite with mltcuda_composite_setup(p_dest = desc.out,
+     * width_dest = desc.width, ...): the rectangle's position inside the A frame is recovered from
+     * (u.composite.dest - desc.out).  u.composite.alpha_a is ignored: whether the running A frame
+     * has an alpha plane at that point follows from in_alpha and the conversions before it.
+     * MLTCUDA_TOP_AFFINE: u.affine.a_image/a_width/a_height ignored (the running frame), rgba only.
+     * MLTCUDA_TOP_LUMA: u.luma.dest/alpha_* ignored; opaque integer wipe, yuv422, progressive. */
     union {
         mltcuda_composite_desc composite;
         mltcuda_affine_desc affine;
@@ -277,6 +284,9 @@ int mltcuda_colour(mltcuda_ctx *ctx, void *dst, uint8_t *dst_alpha, int format, 
 int mltcuda_rescale_yuv422(mltcuda_ctx *ctx, uint8_t *dst, int dst_w, int dst_h,
                            const uint8_t *src, int src_w, int src_h);
 
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
 #ifdef __cplusplus
 }
 #endif

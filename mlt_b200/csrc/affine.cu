@@ -1,0 +1,157 @@
+// affine.cu -- K4: affine transform + sampling + alpha-over (reference
+// src/modules/plus/transition_affine.c:342-409 sliced_proc, src/modules/plus/interp.h:50-334).
+//
+// One thread = 16 bytes of the A image (4 rgba or 2 rgba64 destination pixels).  The inverse
+// mapping runs in double exactly as MapX/MapY (:213-227) do, the sampler in float in the
+// reference's operation order (-fmad=false).  A is only read (and written back) when at least one
+// of the thread's pixels maps inside B, so untouched regions of A cost no HBM traffic; B taps go
+// through the read-only path (L1/L2 catch the 4x / 16x tap re-use of neighbouring pixels).
+// HBM-bound: 12 B per covered pixel (rgba), 24 B (rgba64).
+#include "common.cuh"
+#include "pixel_ops.cuh"
+
+namespace {
+
+struct AffK
+{
+    AffineParams p;
+    uint8_t *a_image;
+    const uint8_t *b_image;
+    int a_width, a_height;
+    size_t a_bs, b_bs;
+    int batch;
+};
+
+template <typename T> __global__ void __launch_bounds__(256) k_affine(AffK K)
+{
+    constexpr int PPT = sizeof(T) == 1 ? 4 : 2;
+    const long long npx = (long long) K.a_width * K.a_height;
+    const long long cpf = (npx + PPT - 1) / PPT;
+    long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= cpf * K.batch)
+        return;
+    int b = (int) (gid / cpf);
+    long long p0 = (gid % cpf) * PPT;
+    int i = (int) (p0 / K.a_width), j = (int) (p0 % K.a_width);
+    const AffineParams &P = K.p;
+
+    // inverse map all pixels first; skip the A traffic when none lands inside B
+    double dxs[PPT], dys[PPT];
+    int hit = 0;
+    {
+        int ii = i, jj = j;
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+            double x = P.lower_x + (double) jj, y = P.lower_y + (double) ii;
+            dxs[k] = (P.m00 * x + P.m01 * y + P.m02) / P.dz + P.x_offset;
+            dys[k] = (P.m10 * x + P.m11 * y + P.m12) / P.dz + P.y_offset;
+            bool in = p0 + k < npx && dxs[k] >= P.minima && dxs[k] <= P.xmax && dys[k] >= P.minima && dys[k] <= P.ymax;
+            hit |= in ? (1 << k) : 0;
+            if (++jj == K.a_width)
+                jj = 0, ii++;
+        }
+    }
+    if (!hit)
+        return;
+    T *q = reinterpret_cast<T *>(K.a_image + b * K.a_bs) + p0 * 4;
+    const T *bimg = reinterpret_cast<const T *>(K.b_image + b * K.b_bs);
+    const bool full = p0 + PPT <= npx;
+    uint32_t qv[PPT][4];
+    if (full) {
+        uint4 a = ld16(q);
+        uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int k = 0; k < PPT; k++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                if (sizeof(T) == 1)
+                    qv[k][c] = (aw[k] >> (8 * c)) & 0xff;
+                else
+                    qv[k][c] = (aw[2 * k + (c >> 1)] >> (16 * (c & 1))) & 0xffff;
+            }
+    } else {
+#pragma unroll
+        for (int k = 0; k < PPT; k++)
+#pragma unroll
+            for (int c = 0; c < 4; c++)
+                qv[k][c] = p0 + k < npx ? q[4 * k + c] : 0;
+    }
+#pragma unroll
+    for (int k = 0; k < PPT; k++) {
+        if (hit & (1 << k)) {
+            float fx = (float) dxs[k], fy = (float) dys[k];
+            if (P.interp == MLTCUDA_INTERP_BL)
+                mc_interp_bl<T>(bimg, P.b_width, P.b_height, fx, fy, P.mix, qv[k], P.b_alpha);
+            else if (P.interp == MLTCUDA_INTERP_NN)
+                mc_interp_nn<T>(bimg, P.b_width, P.b_height, fx, fy, P.mix, qv[k], P.b_alpha);
+            else
+                mc_interp_bc<T>(bimg, P.b_width, P.b_height, fx, fy, P.mix, qv[k], P.b_alpha);
+        }
+    }
+    if (full) {
+        uint32_t ow[4];
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+            if (sizeof(T) == 1)
+                ow[k] = qv[k][0] | (qv[k][1] << 8) | (qv[k][2] << 16) | (qv[k][3] << 24);
+            else
+                ow[2 * k] = qv[k][0] | (qv[k][1] << 16), ow[2 * k + 1] = qv[k][2] | (qv[k][3] << 16);
+        }
+        *reinterpret_cast<uint4 *>(q) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < PPT; k++)
+#pragma unroll
+            for (int c = 0; c < 4; c++)
+                if (p0 + k < npx)
+                    q[4 * k + c] = (T) qv[k][c];
+    }
+}
+
+} // namespace
+
+int mc_fill_affine_params(AffineParams &p, const mltcuda_affine_desc *d)
+{
+    p.m00 = d->matrix[0][0], p.m01 = d->matrix[0][1], p.m02 = d->matrix[0][2];
+    p.m10 = d->matrix[1][0], p.m11 = d->matrix[1][1], p.m12 = d->matrix[1][2];
+    p.lower_x = d->lower_x, p.lower_y = d->lower_y, p.dz = d->dz;
+    p.x_offset = d->x_offset, p.y_offset = d->y_offset;
+    p.minima = d->minima, p.xmax = d->xmax, p.ymax = d->ymax;
+    p.mix = (float) d->mix;
+    p.b_width = d->b_width, p.b_height = d->b_height, p.b_alpha = d->b_alpha, p.interp = d->interp;
+    // The reference samplers read a 2x2 (BL) / 4x4 (BC) footprint clamped to the image; smaller
+    // images make it read out of bounds.  Refuse instead of faulting.
+    int need = d->interp == MLTCUDA_INTERP_BL ? 2 : d->interp == MLTCUDA_INTERP_BC ? 4 : 1;
+    if (d->b_width < need || d->b_height < need) {
+        mltcuda_set_error("affine: B image %dx%d smaller than the %dx%d sampler footprint", d->b_width, d->b_height, need, need);
+        return MLTCUDA_E_BADARG;
+    }
+    return 0;
+}
+
+extern "C" int mltcuda_affine(mltcuda_ctx *ctx, const mltcuda_affine_desc *d)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!d || !d->a_image || !d->b_image, "null image pointer");
+    MC_BADARG(d->format != MLTCUDA_FMT_RGBA && d->format != MLTCUDA_FMT_RGBA64, "affine needs rgba or rgba64");
+    MC_BADARG(d->interp < 0 || d->interp > 2, "bad interpolation");
+    if (d->a_width <= 0 || d->a_height <= 0)
+        return 0;
+    AffK K;
+    if (int e = mc_fill_affine_params(K.p, d))
+        return e;
+    K.a_image = (uint8_t *) d->a_image, K.b_image = (const uint8_t *) d->b_image;
+    K.a_width = d->a_width, K.a_height = d->a_height;
+    K.batch = d->batch > 0 ? d->batch : 1;
+    K.a_bs = d->a_bstride, K.b_bs = d->b_bstride;
+    if (K.batch > 1)
+        MC_BADARG(!K.a_bs, "batch > 1 needs a_bstride");
+    const int ppt = d->format == MLTCUDA_FMT_RGBA ? 4 : 2;
+    long long total = (((long long) d->a_width * d->a_height + ppt - 1) / ppt) * K.batch;
+    if (d->format == MLTCUDA_FMT_RGBA)
+        k_affine<uint8_t><<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);
+    else
+        k_affine<uint16_t><<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);
+    return mc_after_launch(ctx, "k_affine");
+}

@@ -12,6 +12,7 @@ struct mltcuda_ctx
     cudaMemPool_t pool;
     unsigned long long launches;
     int sm_count;
+    uint32_t *noise_tab; // device: skip-ahead tables for the noise producer (lazy)
 };
 
 struct mltcuda_event

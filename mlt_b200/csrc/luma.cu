@@ -1,0 +1,440 @@
+// luma.cu -- K3: luma wipe and dissolve (reference src/modules/core/transition_luma.c:63-292,
+// 327-723) plus scale_luma (src/modules/core/transition_composite.c:497-520).
+//
+// yuv422: one thread = one 16-byte-aligned group of 8 destination pixels (A read-modify-write with
+// 128-bit transactions, B through fetch16, the 16-bit map gathered through the read-only path with
+// the reference's 16.16 fixed-point index).  rgba / rgba64: one thread = 16 bytes of A.
+// The opaque (integer) formula is bit-exact; the translucent (float) formula follows the reference's
+// operation order (-fmad=false), +-1 LSB against its -ffast-math build.  Whether the translucent
+// path is taken is decided ON THE DEVICE by a flag kernel (is_opaque, :34-41) unless the caller
+// forces it, so no host round trip sits between the scan and the blend.
+// HBM-bound: 6 B/px yuv422 (+ map once), 12 B/px rgba, 24 B/px rgba64.
+#include "common.cuh"
+#include "pixel_ops.cuh"
+
+extern void mc_fill_composite_params(CompositeParams &p, const mltcuda_composite_desc *d);
+
+namespace {
+
+// flag |= any(byte != 0xff) over n bytes with the given element stride/offset
+__global__ void __launch_bounds__(256) k_flag_not_ff(const uint8_t *p, size_t n, int stride, int *flag)
+{
+    size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    size_t step = (size_t) gridDim.x * blockDim.x;
+    int bad = 0;
+    for (; i < n; i += step)
+        bad |= p[i * stride] != 0xff;
+    if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0)
+        *flag = 1;
+}
+__global__ void __launch_bounds__(256) k_flag_not_ffff(const uint16_t *p, size_t n, int stride, int *flag)
+{
+    size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    size_t step = (size_t) gridDim.x * blockDim.x;
+    int bad = 0;
+    for (; i < n; i += step)
+        bad |= p[i * stride] != 0xffff;
+    if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0)
+        *flag = 1;
+}
+
+struct LumaK
+{
+    uint8_t *dest;
+    const uint8_t *src;
+    uint8_t *alpha_dest, *alpha_src;
+    const uint16_t *map;
+    int luma_width;
+    int width_src, height_src, width_dest; // after the min() of :376-377
+    int x_diff, y_diff;
+    uint32_t i_softness;
+    float softness, field_pos0, field_pos1;
+    int field_count, invert, alpha_over;
+    const int *flag; // translucent flag on device (may be NULL => forced value)
+    int forced;
+    int rows0;       // rows processed in field 0 (for the running alpha index)
+    int batch;
+    size_t dest_bs, src_bs, ad_bs, as_bs;
+    int cpr;
+    // dissolve
+    float weight;
+    CompositeParams cp;
+};
+
+__device__ __forceinline__ void luma_row_info(const LumaK &K, int i, int &field, int &y_off, int &ordinal)
+{
+    if (K.field_count == 1) {
+        field = 0, y_off = i * K.y_diff, ordinal = i;
+    } else {
+        field = i & 1;
+        int n = i >> 1; // n-th row of its field
+        y_off = (field << 16) + n * K.y_diff;
+        ordinal = field ? K.rows0 + n : n;
+    }
+}
+
+// luma_composite_yuv422 (:327-473) and, with map == NULL, dissolve_yuv422 (:131-190)
+template <bool DISSOLVE> __global__ void __launch_bounds__(256) k_luma_yuv422(LumaK K)
+{
+    long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    long long total = (long long) K.cpr * K.height_src * K.batch;
+    if (gid >= total)
+        return;
+    int c = (int) (gid % K.cpr);
+    long long t = gid / K.cpr;
+    int i = (int) (t % K.height_src);
+    int b = (int) (t / K.height_src);
+    const int translucent = K.flag ? *K.flag : K.forced;
+
+    uintptr_t drow = (uintptr_t) (K.dest + b * K.dest_bs + (size_t) i * K.width_dest * 2);
+    int head = (int) ((drow & 15) >> 1);
+    int j0 = c * 8 - head;
+    if (j0 >= K.width_src)
+        return;
+    int jlo = j0 < 0 ? 0 : j0, jhi = j0 + 8 > K.width_src ? K.width_src : j0 + 8;
+    uint4 *dptr = reinterpret_cast<uint4 *>(drow + 2 * (long) j0);
+    uint4 dv = ld16(dptr);
+    uint32_t d[4] = {dv.x, dv.y, dv.z, dv.w}, s[4];
+    uintptr_t srow = (uintptr_t) (K.src + b * K.src_bs + (size_t) i * K.width_src * 2);
+    fetch16(srow + 2 * (long) j0, srow + 2 * (long) jlo, srow + 2 * (long) jhi, s);
+
+    int field, y_off, ordinal;
+    luma_row_info(K, i, field, y_off, ordinal);
+    const uint16_t *l = DISSOLVE ? nullptr : K.map + (long) (y_off >> 16) * (K.luma_width * K.field_count);
+    const float fpos = field ? K.field_pos1 : K.field_pos0;
+    // running alpha pointers of the reference: one element per processed pixel (:446-449); for a
+    // dissolve they advance by the plane width per row (:181-185, dissolve_slice :97-118)
+    uint8_t *ad = K.alpha_dest ? K.alpha_dest + b * K.ad_bs
+                                     + (DISSOLVE ? (size_t) i * (translucent && K.alpha_over ? K.width_src : K.width_dest)
+                                                 : (size_t) ordinal * K.width_src)
+                               : nullptr;
+    uint8_t *as = K.alpha_src ? K.alpha_src + b * K.as_bs + (DISSOLVE ? (size_t) i * K.width_src : (size_t) ordinal * K.width_src)
+                              : nullptr;
+    uint32_t o[4];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        int j = j0 + k;
+        uint32_t dp = (d[k >> 1] >> ((k & 1) * 16)) & 0xffff;
+        uint32_t sp = (s[k >> 1] >> ((k & 1) * 16)) & 0xffff;
+        uint32_t res = dp;
+        if (j >= jlo && j < jhi) {
+            uint32_t qy = dp & 0xff, qc = dp >> 8, py = sp & 0xff, pc = sp >> 8;
+            if (DISSOLVE) {
+                if (translucent && K.alpha_over) { // composite_line_yuv_float :63-86
+                    float mix_a = (1.0f - K.weight) * (float) (ad ? ad[j] : 255) / 255.f;
+                    float mix_b = K.weight * (float) (as ? as[j] : 255) / 255.f;
+                    if (ad) {
+                        float mix2 = mix_b + mix_a;
+                        ad[j] = (uint8_t) mc_f2u(255 * mix2, 0xff);
+                        if (mix2 != 0.f)
+                            mix_b /= mix2;
+                    }
+                    qy = mc_f2u(py * mix_b + qy * (1.f - mix_b), 0xff);
+                    qc = mc_f2u(pc * mix_b + qc * (1.f - mix_b), 0xff);
+                    res = qy | (qc << 8);
+                } else { // composite_line_yuv(..., mix, NULL, 0, 0) :178-186
+                    uint32_t aak = ad ? ad[j] : 0;
+                    res = mc_composite_px(K.cp, j, dp, sp, as ? as[j] : 255, aak, 0);
+                    if (ad)
+                        ad[j] = (uint8_t) aak;
+                }
+            } else if (translucent) { // :417-451
+                float weight = (float) __ldg(l + ((j * K.x_diff) >> 16)) / 65535.f;
+                float value = mc_smoothstep_f(weight, K.softness + weight, fpos);
+                float mix_a = (1.0f - value) * (float) (ad ? ad[j] : 255) / 255.f;
+                float mix_b = value * (float) (as ? as[j] : 255) / 255.f;
+                uint8_t *at = (K.invert && as) ? as : (!K.invert && ad) ? ad : nullptr;
+                if (at) {
+                    float mix2 = mix_b + mix_a;
+                    if (K.alpha_over) {
+                        at[j] = (uint8_t) mc_f2u(255 * mix2, 0xff);
+                        if (mix2 != 0.f)
+                            mix_b /= mix2;
+                    } else {
+                        float tt = (float) at[j] + 255 * mix_b;
+                        tt = tt < 0.f ? 0.f : tt > 255.f ? 255.f : tt;
+                        at[j] = (uint8_t) mc_f2u(tt, 0xff);
+                    }
+                }
+                qy = mc_f2u(py * mix_b + qy * (1.f - mix_b), 0xff);
+                qc = mc_f2u(pc * mix_b + qc * (1.f - mix_b), 0xff);
+                res = qy | (qc << 8);
+            } else { // :452-463
+                uint32_t weight = __ldg(l + ((j * K.x_diff) >> 16));
+                uint32_t value = (uint32_t) mc_smoothstep((int32_t) weight, (int32_t) (K.i_softness + weight),
+                                                          (uint32_t) ((1 << 16) * fpos));
+                qy = (py * value + qy * ((1u << 16) - value)) >> 16;
+                qc = (pc * value + qc * ((1u << 16) - value)) >> 16;
+                res = (qy & 0xff) | ((qc & 0xff) << 8);
+            }
+        }
+        if (k & 1)
+            o[k >> 1] |= res << 16;
+        else
+            o[k >> 1] = res;
+    }
+    if (jlo == j0 && jhi == j0 + 8) {
+        *dptr = make_uint4(o[0], o[1], o[2], o[3]);
+    } else {
+        uint16_t *d16 = reinterpret_cast<uint16_t *>(dptr);
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+            if (j0 + k >= jlo && j0 + k < jhi)
+                d16[k] = (uint16_t) (o[k >> 1] >> ((k & 1) * 16));
+    }
+}
+
+// luma_composite_rgba32/_rgba64 (:475-723) and dissolve_slice_rgba32/_rgba64 (:192-265).
+// T = uint8_t: 4 px per thread; uint16_t: 2 px per thread (16 bytes of A either way).
+template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256) k_luma_rgba(LumaK K)
+{
+    constexpr int PPT = sizeof(T) == 1 ? 4 : 2;
+    const float maxv = PxTraits<T>::maxv;
+    const uint32_t mask = PxTraits<T>::mask;
+    const int w = K.width_src, h = K.height_src;
+    const long long npx = (long long) w * h;
+    const long long cpf = (npx + PPT - 1) / PPT;
+    long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= cpf * K.batch)
+        return;
+    int b = (int) (gid / cpf);
+    long long p0 = (gid % cpf) * PPT;
+    const int translucent = K.flag ? *K.flag : K.forced;
+    T *q = reinterpret_cast<T *>(K.dest + b * K.dest_bs) + p0 * 4;
+    const T *p = reinterpret_cast<const T *>(K.src + b * K.src_bs) + p0 * 4;
+    uint32_t qv[PPT][4], pv[PPT][4];
+    const bool full = p0 + PPT <= npx;
+    if (full) {
+        uint4 a = ld16(q), s = ldg16(p);
+        uint32_t aw[4] = {a.x, a.y, a.z, a.w}, sw[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+        for (int k = 0; k < PPT; k++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                if (sizeof(T) == 1)
+                    qv[k][c] = (aw[k] >> (8 * c)) & 0xff, pv[k][c] = (sw[k] >> (8 * c)) & 0xff;
+                else
+                    qv[k][c] = (aw[2 * k + (c >> 1)] >> (16 * (c & 1))) & 0xffff,
+                    pv[k][c] = (sw[2 * k + (c >> 1)] >> (16 * (c & 1))) & 0xffff;
+            }
+    } else {
+#pragma unroll
+        for (int k = 0; k < PPT; k++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                bool ok = p0 + k < npx;
+                qv[k][c] = ok ? q[4 * k + c] : 0, pv[k][c] = ok ? p[4 * k + c] : 0;
+            }
+    }
+    int i = (int) (p0 / w), j = (int) (p0 % w);
+#pragma unroll
+    for (int k = 0; k < PPT; k++) {
+        if (p0 + k < npx) {
+            if (DISSOLVE) {
+                float mix_a = (1.0f - K.weight) * (float) qv[k][3] / maxv;
+                float mix_b = K.weight * (float) pv[k][3] / maxv;
+                float mix2 = mix_b + mix_a;
+                if (mix2 != 0.f)
+                    mix_b /= mix2;
+#pragma unroll
+                for (int c = 0; c < 3; c++)
+                    qv[k][c] = mc_f2u(pv[k][c] * mix_b + qv[k][c] * (1.f - mix_b), mask);
+                qv[k][3] = mc_f2u(maxv * mix2, mask);
+            } else {
+                int field, y_off, ordinal;
+                luma_row_info(K, i, field, y_off, ordinal);
+                const float fpos = field ? K.field_pos1 : K.field_pos0;
+                uint32_t lw = __ldg(K.map + (long) (y_off >> 16) * (K.luma_width * K.field_count) + ((j * K.x_diff) >> 16));
+                if (translucent) {
+                    float weight = (float) lw / 65535.f;
+                    float value = mc_smoothstep_f(weight, K.softness + weight, fpos);
+                    float mix_a = (1.0f - value) * (float) qv[k][3] / maxv;
+                    float mix_b = value * (float) pv[k][3] / maxv;
+                    float mix2 = mix_b + mix_a;
+                    if (K.alpha_over) {
+                        qv[k][3] = mc_f2u(maxv * mix2, mask);
+                        if (mix2 != 0.f)
+                            mix_b /= mix2;
+                    } else {
+                        float tt = (float) qv[k][3] + maxv * mix_b;
+                        tt = tt < 0.f ? 0.f : tt > maxv ? maxv : tt;
+                        qv[k][3] = mc_f2u(tt, mask);
+                    }
+#pragma unroll
+                    for (int c = 0; c < 3; c++)
+                        qv[k][c] = mc_f2u(pv[k][c] * mix_b + qv[k][c] * (1.f - mix_b), mask);
+                } else {
+                    uint32_t value = (uint32_t) mc_smoothstep((int32_t) lw, (int32_t) (K.i_softness + lw),
+                                                              (uint32_t) ((1 << 16) * fpos));
+#pragma unroll
+                    for (int c = 0; c < 3; c++)
+                        qv[k][c] = ((pv[k][c] * value + qv[k][c] * ((1u << 16) - value)) >> 16) & mask;
+                }
+            }
+        }
+        if (++j == w)
+            j = 0, i++;
+    }
+    if (full) {
+        uint32_t ow[4];
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+            if (sizeof(T) == 1)
+                ow[k] = qv[k][0] | (qv[k][1] << 8) | (qv[k][2] << 16) | (qv[k][3] << 24);
+            else
+                ow[2 * k] = qv[k][0] | (qv[k][1] << 16), ow[2 * k + 1] = qv[k][2] | (qv[k][3] << 16);
+        }
+        *reinterpret_cast<uint4 *>(q) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < PPT; k++)
+#pragma unroll
+            for (int c = 0; c < 4; c++)
+                if (p0 + k < npx)
+                    q[4 * k + c] = (T) qv[k][c];
+    }
+}
+
+__global__ void __launch_bounds__(256) k_scale_luma(uint16_t *dst, int dw, int dh, const uint16_t *src, int sw,
+                                                    int x_step, int y_step, int invert_xor)
+{
+    long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (long long) dw * dh)
+        return;
+    int j = (int) (gid % dw), i = (int) (gid / dw);
+    dst[gid] = __ldg(src + (long) ((i * y_step) >> 16) * sw + ((j * x_step) >> 16)) ^ (uint16_t) invert_xor;
+}
+
+} // namespace
+
+extern "C" int mltcuda_scale_luma(mltcuda_ctx *ctx, uint16_t *dst, int dw, int dh, const uint16_t *src,
+                                  int sw, int sh, int invert_xor)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!dst || !src || dw <= 0 || dh <= 0 || sw <= 0 || sh <= 0, "bad argument");
+    k_scale_luma<<<mc_blocks((long long) dw * dh, 256), 256, 0, ctx->stream>>>(dst, dw, dh, src, sw, (sw << 16) / dw,
+                                                                            (sh << 16) / dh, invert_xor);
+    return mc_after_launch(ctx, "k_scale_luma");
+}
+
+extern "C" int mltcuda_luma(mltcuda_ctx *ctx, const mltcuda_luma_desc *d)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!d || !d->dest || !d->src, "null image pointer");
+    const int fmt = d->format;
+    MC_BADARG(fmt != MLTCUDA_FMT_YUV422 && fmt != MLTCUDA_FMT_RGBA && fmt != MLTCUDA_FMT_RGBA64, "bad format");
+    if (d->width == 0 || d->height == 0) // :369-370
+        return 0;
+    LumaK K = {};
+    K.dest = (uint8_t *) d->dest, K.src = (const uint8_t *) d->src;
+    K.alpha_dest = d->alpha_dest, K.alpha_src = d->alpha_src;
+    K.map = d->map, K.luma_width = d->luma_width;
+    K.batch = d->batch > 0 ? d->batch : 1;
+    K.dest_bs = d->dest_bstride, K.src_bs = d->src_bstride, K.ad_bs = d->alpha_dest_bstride, K.as_bs = d->alpha_src_bstride;
+    if (K.batch > 1)
+        MC_BADARG(!K.dest_bs || !K.src_bs, "batch > 1 needs dest/src bstride");
+    K.invert = d->invert, K.alpha_over = d->alpha_over;
+    K.softness = d->softness;
+    K.i_softness = (uint32_t) (d->softness * (1 << 16));
+    K.field_count = d->field_order < 0 ? 1 : 2;
+    K.field_pos0 = (d->pos + ((d->field_order == 0 ? 1 : 0) * d->frame_delta * 0.5f)) * (1.f + d->softness);
+    K.field_pos1 = (d->pos + ((d->field_order == 0 ? 0 : 1) * d->frame_delta * 0.5f)) * (1.f + d->softness);
+    const bool dissolve = d->map == nullptr;
+    K.weight = d->pos;
+
+    // translucency flag
+    int *flag = nullptr;
+    K.forced = d->translucent > 0;
+    if (d->translucent < 0) {
+        MC_BADARG(K.batch != 1, "device-side opacity scan supports batch == 1");
+        flag = (int *) mltcuda_malloc(ctx, sizeof(int));
+        if (!flag)
+            return (int) cudaErrorMemoryAllocation;
+        MC_CHECK(cudaMemsetAsync(flag, 0, sizeof(int), ctx->stream));
+        const int grid = ctx->sm_count * 8;
+        if (fmt == MLTCUDA_FMT_YUV422) {
+            if (d->alpha_dest) {
+                k_flag_not_ff<<<grid, 256, 0, ctx->stream>>>(d->alpha_dest, (size_t) d->width_dest * d->height_dest, 1, flag);
+                mc_after_launch(ctx, "k_flag_not_ff");
+            }
+            if (d->alpha_src) {
+                k_flag_not_ff<<<grid, 256, 0, ctx->stream>>>(d->alpha_src, (size_t) d->width_src * d->height_src, 1, flag);
+                mc_after_launch(ctx, "k_flag_not_ff");
+            }
+        } else if (fmt == MLTCUDA_FMT_RGBA) {
+            k_flag_not_ff<<<grid, 256, 0, ctx->stream>>>((const uint8_t *) d->dest + 3, (size_t) d->width_dest * d->height_dest, 4, flag);
+            k_flag_not_ff<<<grid, 256, 0, ctx->stream>>>((const uint8_t *) d->src + 3, (size_t) d->width_src * d->height_src, 4, flag);
+            mc_after_launch(ctx, "k_flag_not_ff");
+            mc_after_launch(ctx, "k_flag_not_ff");
+        } else {
+            k_flag_not_ffff<<<grid, 256, 0, ctx->stream>>>((const uint16_t *) d->dest + 3, (size_t) d->width_dest * d->height_dest, 4, flag);
+            k_flag_not_ffff<<<grid, 256, 0, ctx->stream>>>((const uint16_t *) d->src + 3, (size_t) d->width_src * d->height_src, 4, flag);
+            mc_after_launch(ctx, "k_flag_not_ffff");
+            mc_after_launch(ctx, "k_flag_not_ffff");
+        }
+        K.flag = flag;
+    }
+
+    int rc = 0;
+    if (fmt == MLTCUDA_FMT_YUV422) {
+        K.width_dest = d->width_dest;
+        K.width_src = d->width_src > d->width_dest ? d->width_dest : d->width_src;
+        K.height_src = d->height_src > d->height_dest ? d->height_dest : d->height_src;
+        if (dissolve) {
+            // dissolve_yuv422 :131-190: mix = weight * (1<<16), composite_line_yuv per row.
+            mltcuda_composite_desc cd = {};
+            cd.width = K.width_src, cd.weight = (int) (d->pos * (1 << 16));
+            cd.alpha_b = d->alpha_src, cd.alpha_a = d->alpha_dest;
+            mc_fill_composite_params(K.cp, &cd);
+        } else {
+            MC_BADARG(d->luma_width <= 0 || d->luma_height <= 0, "bad luma map size");
+            K.x_diff = (d->luma_width << 16) / d->width;
+            K.y_diff = (d->luma_height << 16) / d->height;
+        }
+        K.rows0 = (K.height_src + 1) / 2;
+        K.cpr = (K.width_src + 14) / 8;
+        long long total = (long long) K.cpr * K.height_src * K.batch;
+        if (total > 0) {
+            if (dissolve)
+                k_luma_yuv422<true><<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);
+            else
+                k_luma_yuv422<false><<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);
+            rc = mc_after_launch(ctx, "k_luma_yuv422");
+        }
+    } else {
+        // :496-499 / :620-623: sizes must match
+        if (d->width_src != d->width_dest || d->height_src != d->height_dest || d->width_src == 0 || d->height_src == 0) {
+            if (flag)
+                mltcuda_free(ctx, flag);
+            mltcuda_set_error("Unable to dissolve incompatible images");
+            return MLTCUDA_E_BADARG;
+        }
+        K.width_src = d->width_dest, K.height_src = d->height_dest, K.width_dest = d->width_dest;
+        if (!dissolve) {
+            MC_BADARG(d->luma_width <= 0 || d->luma_height <= 0, "bad luma map size");
+            K.x_diff = (d->luma_width << 16) / d->width_dest;
+            K.y_diff = (d->luma_height << 16) / d->height_dest;
+        }
+        K.rows0 = (K.height_src + 1) / 2;
+        const int ppt = fmt == MLTCUDA_FMT_RGBA ? 4 : 2;
+        long long total = (((long long) K.width_src * K.height_src + ppt - 1) / ppt) * K.batch;
+        unsigned blocks = mc_blocks(total, 256);
+        if (fmt == MLTCUDA_FMT_RGBA) {
+            if (dissolve)
+                k_luma_rgba<uint8_t, true><<<blocks, 256, 0, ctx->stream>>>(K);
+            else
+                k_luma_rgba<uint8_t, false><<<blocks, 256, 0, ctx->stream>>>(K);
+        } else {
+            if (dissolve)
+                k_luma_rgba<uint16_t, true><<<blocks, 256, 0, ctx->stream>>>(K);
+            else
+                k_luma_rgba<uint16_t, false><<<blocks, 256, 0, ctx->stream>>>(K);
+        }
+        rc = mc_after_launch(ctx, "k_luma_rgba");
+    }
+    if (flag)
+        mltcuda_free(ctx, flag);
+    return rc;
+}

@@ -1,0 +1,239 @@
+// producers.cu -- device-side synthetic producers and normalisers, so the
+// benchmark configurations' sources never cross PCIe:
+//   noise  : reference src/modules/core/producer_noise.c:37-51,108-123
+//   colour : reference src/modules/core/producer_colour.c:140-205,228-236
+//   rescale: reference src/modules/core/filter_rescale.c:48-120 (nearest-neighbour yuv422)
+//
+// The noise producer's two 16-bit multiply-with-carry generators are sequential in the reference
+// (and the buffer is filled from its END backwards).  A lag-1 MWC with multiplier a and base 2^16
+// satisfies t[n+1] = a*t[n] mod (a*2^16-1) once the state is below the modulus (true from the 2nd
+// step on), so the state at step n is a^(n-2)*t[2] mod m: each thread jumps straight to the state
+// of the last pixel of its 8-pixel group with three table look-ups (a^n split into 12+12+8 bit
+// digits) and then steps the generators 8 times exactly like the reference.  Bit-exact.
+#include "common.cuh"
+#include "pixel_ops.cuh"
+
+namespace {
+
+constexpr uint32_t MWC_A = 18000u, MWC_B = 30903u;
+constexpr uint64_t MOD_A = (uint64_t) MWC_A * 65536u - 1, MOD_B = (uint64_t) MWC_B * 65536u - 1;
+// table layout (uint32): [gen][level0: 4096][level1: 4096][level2: 256]
+constexpr int TAB_PER_GEN = 4096 + 4096 + 256;
+
+__device__ __forceinline__ uint32_t mwc_pow(const uint32_t *tab, uint64_t mod, uint64_t n)
+{
+    uint64_t r = __ldg(tab + (n & 4095));
+    r = r * __ldg(tab + 4096 + ((n >> 12) & 4095)) % mod;
+    r = r * __ldg(tab + 8192 + ((n >> 24) & 255)) % mod;
+    return (uint32_t) r;
+}
+
+__global__ void __launch_bounds__(256) k_noise(uint8_t *dst, long long npx, uint32_t x2, uint32_t y2, uint32_t x0,
+                                               uint32_t y0, const uint32_t *tab, int batch, size_t bs,
+                                               int position)
+{
+    const long long cpf = (npx + 7) / 8;
+    long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= cpf * batch)
+        return;
+    int b = (int) (gid / cpf);
+    long long c = gid % cpf;
+    // batch frame b is timeline position `position + b`: re-seed (init_seed :37-43)
+    if (b) {
+        uint32_t p = (uint32_t) (position + b);
+        x0 = 521288629u + p - (p << 16), y0 = 362436069u - p + (p << 16);
+        uint32_t x = x0, y = y0;
+        for (int k = 0; k < 2; k++)
+            x = MWC_A * (x & 65535) + (x >> 16), y = MWC_B * (y & 65535) + (y >> 16);
+        x2 = x, y2 = y;
+    }
+    long long hi = c * 8 + 7 < npx ? c * 8 + 7 : npx - 1; // last pixel of the group
+    long long n = npx - hi;                               // its generation step (1-based)
+    uint32_t x, y;
+    if (n >= 2) {
+        x = (uint32_t) ((uint64_t) mwc_pow(tab, MOD_A, (uint64_t) n - 2) * x2 % MOD_A);
+        y = (uint32_t) ((uint64_t) mwc_pow(tab + TAB_PER_GEN, MOD_B, (uint64_t) n - 2) * y2 % MOD_B);
+    } else { // n == 1
+        x = MWC_A * (x0 & 65535) + (x0 >> 16), y = MWC_B * (y0 & 65535) + (y0 >> 16);
+    }
+    uint32_t w[4] = {0, 0, 0, 0};
+    int cnt = (int) (hi - c * 8) + 1;
+#pragma unroll
+    for (int k = 7; k >= 0; k--) {
+        if (k < cnt) {
+            uint32_t value = ((x << 16) + (y & 65535)) & 0xff;
+            value = value < 16 ? 16 : value > 240 ? 240 : value;
+            w[k >> 1] |= (value | (128u << 8)) << ((k & 1) * 16);
+            x = MWC_A * (x & 65535) + (x >> 16), y = MWC_B * (y & 65535) + (y >> 16);
+        }
+    }
+    uint8_t *d = dst + b * bs + c * 16;
+    if (cnt == 8) {
+        *reinterpret_cast<uint4 *>(d) = make_uint4(w[0], w[1], w[2], w[3]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+            if (k < cnt)
+                reinterpret_cast<uint16_t *>(d)[k] = (uint16_t) (w[k >> 1] >> ((k & 1) * 16));
+    }
+}
+
+__global__ void __launch_bounds__(256) k_fill16(uint4 *dst, size_t n16, uint4 v)
+{
+    size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n16)
+        dst[i] = v;
+}
+
+__global__ void __launch_bounds__(256) k_colour_yuv422(uint8_t *dst, int width, int height, uint32_t y, uint32_t u, uint32_t v)
+{
+    long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    int ppr = (width + 1) / 2;
+    if (gid >= (long long) ppr * height)
+        return;
+    int pi = (int) (gid % ppr), line = (int) (gid / ppr);
+    uint8_t *d = dst + (size_t) line * width * 2 + 4 * (size_t) pi;
+    d[0] = y, d[1] = u;
+    if (2 * pi + 1 < width)
+        d[2] = y, d[3] = v;
+}
+
+// filter_scale (:48-120)
+__global__ void __launch_bounds__(256) k_rescale_yuv422(uint8_t *dst, int ow, int oh, const uint8_t *src, int istride,
+                                                        long in_middle, int scale_width, int scale_height, int outer,
+                                                        int bottom, int ncols, int nrows)
+{
+    long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (long long) ncols * nrows)
+        return;
+    int pc = (int) (gid % ncols), row = (int) (gid / ncols); // pc = output pixel pair
+    int dy = -bottom + row * scale_height;
+    int dx = -outer + 2 * pc * scale_width;
+    const uint8_t *in_line = src + in_middle + (long) (dy >> 16) * istride;
+    uint8_t *o = dst + (size_t) row * ow * 2 + 4 * (size_t) pc;
+    int base = dx >> 15;
+    base &= 0xfffffffe;
+    uint32_t r = in_line[base];
+    base &= 0xfffffffc;
+    r |= (uint32_t) in_line[base + 1] << 8;
+    dx += scale_width;
+    base = dx >> 15;
+    base &= 0xfffffffe;
+    r |= (uint32_t) in_line[base] << 16;
+    base &= 0xfffffffc;
+    r |= (uint32_t) in_line[base + 3] << 24;
+    *reinterpret_cast<uint32_t *>(o) = r;
+}
+
+int ensure_noise_tab(mltcuda_ctx *ctx)
+{
+    if (ctx->noise_tab)
+        return 0;
+    static uint32_t host[2 * TAB_PER_GEN];
+    const uint64_t mods[2] = {MOD_A, MOD_B};
+    const uint64_t as[2] = {MWC_A, MWC_B};
+    for (int g = 0; g < 2; g++) {
+        uint32_t *t = host + g * TAB_PER_GEN;
+        uint64_t m = mods[g], v = 1;
+        for (int i = 0; i < 4096; i++)
+            t[i] = (uint32_t) v, v = v * as[g] % m; // v = a^4096 at the end
+        uint64_t s1 = v;
+        v = 1;
+        for (int i = 0; i < 4096; i++)
+            t[4096 + i] = (uint32_t) v, v = v * s1 % m; // v = a^(2^24)
+        uint64_t s2 = v;
+        v = 1;
+        for (int i = 0; i < 256; i++)
+            t[8192 + i] = (uint32_t) v, v = v * s2 % m;
+    }
+    MC_CHECK(cudaMalloc(&ctx->noise_tab, sizeof(host)));
+    MC_CHECK(cudaMemcpy(ctx->noise_tab, host, sizeof(host), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+} // namespace
+
+extern "C" int mltcuda_noise(mltcuda_ctx *ctx, uint8_t *dst, int width, int height, int position, int batch,
+                             size_t dst_bstride)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!dst || width < 0 || height < 0, "bad argument");
+    MC_BADARG(((uintptr_t) dst & 15) || (dst_bstride & 15), "noise destination must be 16-byte aligned");
+    long long npx = (long long) width * height;
+    if (npx == 0)
+        return 0;
+    if (batch <= 0)
+        batch = 1;
+    if (int e = ensure_noise_tab(ctx))
+        return e;
+    uint32_t p = (uint32_t) position;
+    uint32_t x0 = 521288629u + p - (p << 16), y0 = 362436069u - p + (p << 16);
+    uint32_t x = x0, y = y0;
+    for (int k = 0; k < 2; k++)
+        x = MWC_A * (x & 65535) + (x >> 16), y = MWC_B * (y & 65535) + (y >> 16);
+    long long total = ((npx + 7) / 8) * batch;
+    k_noise<<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(dst, npx, x, y, x0, y0, ctx->noise_tab, batch, dst_bstride, position);
+    return mc_after_launch(ctx, "k_noise");
+}
+
+extern "C" int mltcuda_colour(mltcuda_ctx *ctx, void *dst, uint8_t *dst_alpha, int format, int width, int height,
+                              uint8_t r, uint8_t g, uint8_t b, uint8_t a)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!dst || width < 0 || height < 0, "bad argument");
+    size_t n = (size_t) width * height;
+    if (n == 0)
+        return 0;
+    if (format == MLTCUDA_FMT_YUV422) {
+        int y, u, v;
+        y = ((263 * r + 516 * g + 100 * b) >> 10) + 16;
+        u = ((-152 * r - 300 * g + 450 * b) >> 10) + 128;
+        v = ((450 * r - 377 * g - 73 * b) >> 10) + 128;
+        long long total = (long long) ((width + 1) / 2) * height;
+        k_colour_yuv422<<<mc_blocks(total, 256), 256, 0, ctx->stream>>>((uint8_t *) dst, width, height, y & 0xff, u & 0xff, v & 0xff);
+        if (int e = mc_after_launch(ctx, "k_colour_yuv422"))
+            return e;
+        if (dst_alpha)
+            MC_CHECK(cudaMemsetAsync(dst_alpha, a, n, ctx->stream));
+        return 0;
+    }
+    uint4 v;
+    size_t bytes;
+    if (format == MLTCUDA_FMT_RGBA) {
+        uint32_t p = r | (g << 8) | (b << 16) | ((uint32_t) a << 24);
+        v = make_uint4(p, p, p, p), bytes = n * 4;
+    } else if (format == MLTCUDA_FMT_RGBA64) {
+        uint32_t lo = ((r << 8) + r) | (((g << 8) + g) << 16), hi = ((b << 8) + b) | ((uint32_t) ((a << 8) + a) << 16);
+        v = make_uint4(lo, hi, lo, hi), bytes = n * 8;
+    } else {
+        mltcuda_set_error("colour: unsupported format %d", format);
+        return MLTCUDA_E_UNSUPPORTED;
+    }
+    MC_BADARG((uintptr_t) dst & 15, "colour destination must be 16-byte aligned");
+    size_t n16 = (bytes + 15) / 16; // tail slack of mltcuda_malloc absorbs the round-up
+    k_fill16<<<mc_blocks(n16, 256), 256, 0, ctx->stream>>>((uint4 *) dst, n16, v);
+    return mc_after_launch(ctx, "k_fill16");
+}
+
+extern "C" int mltcuda_rescale_yuv422(mltcuda_ctx *ctx, uint8_t *dst, int ow, int oh, const uint8_t *src, int iw, int ih)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!dst || !src || ow <= 0 || oh <= 0 || iw <= 0 || ih <= 0, "bad argument");
+    int istride = iw * 2;
+    iw -= iw % 4;
+    int out_x_range = ow / 2, out_y_range = oh / 2, in_x_range = iw / 2, in_y_range = ih / 2;
+    long in_middle = (long) istride * in_y_range + in_x_range * 2;
+    int scale_width = (iw << 16) / ow, scale_height = (ih << 16) / oh;
+    int outer = out_x_range * scale_width, bottom = out_y_range * scale_height;
+    if (scale_width <= 0 || scale_height <= 0 || outer <= 0 || bottom <= 0)
+        return 0;
+    // loop trip counts of :93-110: dy from -bottom step scale_height while < bottom; dx advances twice per pair
+    int nrows = (2 * bottom + scale_height - 1) / scale_height;
+    int ncols = (2 * outer + 2 * scale_width - 1) / (2 * scale_width);
+    k_rescale_yuv422<<<mc_blocks((long long) ncols * nrows, 256), 256, 0, ctx->stream>>>(dst, ow, oh, src, istride, in_middle,
+                                                                                     scale_width, scale_height, outer, bottom, ncols, nrows);
+    return mc_after_launch(ctx, "k_rescale_yuv422");
+}

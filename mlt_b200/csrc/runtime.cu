@@ -59,6 +59,7 @@ mltcuda_ctx *mltcuda_ctx_create(int device)
     mltcuda_ctx *ctx = new mltcuda_ctx();
     ctx->device = device;
     ctx->launches = 0;
+    ctx->noise_tab = nullptr;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
         mltcuda_set_error("cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError()));
         delete ctx;
@@ -78,6 +79,8 @@ void mltcuda_ctx_destroy(mltcuda_ctx *ctx)
         return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->noise_tab)
+        cudaFree(ctx->noise_tab);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

@@ -1,0 +1,278 @@
+// tractor.cu -- K5: fused multi-track pass.  Replaces the chain of full-frame read-modify-write
+// passes (one per transition, plus a format conversion between neighbours that want different
+// formats) that the reference's tractor / transition / convert plumbing produces
+// (src/framework/mlt_tractor.c:348-424, mlt_transition.c:328-381, mlt_frame.c:501-541,839-998;
+// SURVEY 3.4) by ONE kernel: each thread carries an 8-pixel group of the A frame in registers
+// through the whole op list (composite rows, yuv422<->rgba conversions, affine sampling, opaque
+// luma wipe) and writes the result once.  Every op is pointwise in A (B layers are gathered), and
+// the group is pair-aligned, so all intermediate integer steps -- chroma pair averaging, clamps,
+// alpha-plane creation -- are reproduced exactly: the output is byte-identical to running the ops
+// as separate launches.  HBM traffic: A read once + written once + each layer's pixels once.
+#include "common.cuh"
+#include "pixel_ops.cuh"
+
+extern void mc_fill_composite_params(CompositeParams &p, const mltcuda_composite_desc *d);
+extern int mc_fill_affine_params(AffineParams &p, const mltcuda_affine_desc *d);
+
+namespace {
+
+struct TCompOp
+{
+    CompositeParams cp;
+    const uint8_t *src, *alpha_b;
+    const uint16_t *luma;
+    int x, y, rows, row_step;
+    long stride_src, stride_ab;
+    size_t src_bs, ab_bs, luma_bs;
+};
+struct TAffOp
+{
+    AffineParams ap;
+    const uint8_t *b_image;
+    size_t b_bs;
+};
+struct TLumaOp
+{
+    const uint8_t *src;
+    const uint16_t *map;
+    int luma_width, width_src, height_src, x_diff, y_diff;
+    uint32_t i_softness, step;
+    size_t src_bs;
+};
+struct TOp
+{
+    int kind, to_format;
+    union {
+        TCompOp c;
+        TAffOp a;
+        TLumaOp l;
+    };
+};
+struct TractorK
+{
+    int width, height, in_format, n_ops, batch;
+    const uint8_t *in, *in_alpha;
+    uint8_t *out, *out_alpha;
+    size_t in_bs, ia_bs, out_bs, oa_bs;
+    TOp ops[MLTCUDA_TRACTOR_MAX_OPS];
+};
+
+__global__ void __launch_bounds__(256) k_tractor(const __grid_constant__ TractorK K)
+{
+    const int cpr = K.width >> 3;
+    long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
+    long long total = (long long) cpr * K.height * K.batch;
+    if (gid >= total)
+        return;
+    const int c = (int) (gid % cpr);
+    long long t = gid / cpr;
+    const int r = (int) (t % K.height);
+    const int b = (int) (t / K.height);
+    const int col0 = c * 8;
+    const size_t pix0 = (size_t) r * K.width + col0;
+
+    uint32_t yuv[4] = {0, 0, 0, 0}, rgba[8], al[2] = {0xffffffffu, 0xffffffffu};
+    int fmt = K.in_format;
+    int has_alpha = 0;
+    if (fmt == MLTCUDA_FMT_YUV422) {
+        uint4 v = ldg16(K.in + b * K.in_bs + pix0 * 2);
+        yuv[0] = v.x, yuv[1] = v.y, yuv[2] = v.z, yuv[3] = v.w;
+        if (K.in_alpha) {
+            uint2 a = ldg8(K.in_alpha + b * K.ia_bs + pix0);
+            al[0] = a.x, al[1] = a.y, has_alpha = 1;
+        }
+    } else {
+        const uint8_t *p = K.in + b * K.in_bs + pix0 * 4;
+        uint4 v0 = ldg16(p), v1 = ldg16(p + 16);
+        rgba[0] = v0.x, rgba[1] = v0.y, rgba[2] = v0.z, rgba[3] = v0.w;
+        rgba[4] = v1.x, rgba[5] = v1.y, rgba[6] = v1.z, rgba[7] = v1.w;
+    }
+
+    for (int oi = 0; oi < K.n_ops; oi++) {
+        const TOp &op = K.ops[oi];
+        if (op.kind == MLTCUDA_TOP_COMPOSITE) {
+            const TCompOp &C = op.c;
+            int rrel = r - C.y;
+            if (rrel < 0 || (C.row_step == 2 && (rrel & 1)))
+                continue;
+            int rr = C.row_step == 2 ? rrel >> 1 : rrel;
+            int j0 = col0 - C.x;
+            if (rr >= C.rows || j0 + 8 <= 0 || j0 >= C.cp.width)
+                continue;
+            int jlo = j0 < 0 ? 0 : j0, jhi = j0 + 8 > C.cp.width ? C.cp.width : j0 + 8;
+            uint32_t s[4], ab[2] = {0, 0}, lum[4] = {0, 0, 0, 0};
+            uintptr_t srow = (uintptr_t) (C.src + b * C.src_bs + rr * C.stride_src);
+            fetch16(srow + 2 * (long) j0, srow + 2 * (long) jlo, srow + 2 * (long) jhi, s);
+            if (C.cp.has_ab) {
+                uintptr_t arow = (uintptr_t) (C.alpha_b + b * C.ab_bs + rr * C.stride_ab);
+                fetch8(arow + j0, arow + jlo, arow + jhi, ab);
+            }
+            if (C.cp.has_luma) {
+                uintptr_t lrow = (uintptr_t) (C.luma + b * (C.luma_bs / 2) + rr * C.stride_ab);
+                fetch16(lrow + 2 * (long) j0, lrow + 2 * (long) jlo, lrow + 2 * (long) jhi, lum);
+            }
+            uint32_t o[4], oa[2] = {0, 0};
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                uint32_t dp = (yuv[k >> 1] >> ((k & 1) * 16)) & 0xffff;
+                uint32_t sp = (s[k >> 1] >> ((k & 1) * 16)) & 0xffff;
+                uint32_t abk = (ab[k >> 2] >> ((k & 3) * 8)) & 0xff;
+                uint32_t aak = (al[k >> 2] >> ((k & 3) * 8)) & 0xff;
+                uint32_t lk = (lum[k >> 1] >> ((k & 1) * 16)) & 0xffff;
+                int j = j0 + k;
+                uint32_t res = dp;
+                if (j >= jlo && j < jhi)
+                    res = mc_composite_px(C.cp, j, dp, sp, abk, aak, lk);
+                if (k & 1)
+                    o[k >> 1] |= res << 16;
+                else
+                    o[k >> 1] = res;
+                oa[k >> 2] |= aak << ((k & 3) * 8);
+            }
+            yuv[0] = o[0], yuv[1] = o[1], yuv[2] = o[2], yuv[3] = o[3];
+            if (has_alpha)
+                al[0] = oa[0], al[1] = oa[1];
+        } else if (op.kind == MLTCUDA_TOP_CONVERT) {
+            if (op.to_format == MLTCUDA_FMT_RGBA) { // filter_imageconvert.c:58-111
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    uint32_t a0 = has_alpha ? (al[k >> 1] >> ((k & 1) * 16)) & 0xff : 0xff;
+                    uint32_t a1 = has_alpha ? (al[k >> 1] >> ((k & 1) * 16 + 8)) & 0xff : 0xff;
+                    mc_yuyv_to_rgba2(yuv[k], a0, a1, rgba[2 * k], rgba[2 * k + 1]);
+                }
+                fmt = MLTCUDA_FMT_RGBA, has_alpha = 0; // convert_image clears the alpha plane (:475-477)
+            } else { // filter_imageconvert.c:144-184: creates the alpha plane
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    yuv[k] = mc_rgba2_to_yuyv(rgba[2 * k], rgba[2 * k + 1]);
+                al[0] = (rgba[0] >> 24) | ((rgba[1] >> 24) << 8) | ((rgba[2] >> 24) << 16) | ((rgba[3] >> 24) << 24);
+                al[1] = (rgba[4] >> 24) | ((rgba[5] >> 24) << 8) | ((rgba[6] >> 24) << 16) | ((rgba[7] >> 24) << 24);
+                fmt = MLTCUDA_FMT_YUV422, has_alpha = 1;
+            }
+        } else if (op.kind == MLTCUDA_TOP_AFFINE) {
+            const uint8_t *bimg = op.a.b_image + b * op.a.b_bs;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                uint32_t d[4] = {rgba[k] & 0xff, (rgba[k] >> 8) & 0xff, (rgba[k] >> 16) & 0xff, rgba[k] >> 24};
+                if (mc_affine_px<uint8_t>(op.a.ap, bimg, col0 + k, r, d))
+                    rgba[k] = d[0] | (d[1] << 8) | (d[2] << 16) | (d[3] << 24);
+            }
+        } else if (op.kind == MLTCUDA_TOP_LUMA) { // transition_luma.c:452-463, progressive
+            const TLumaOp &L = op.l;
+            if (r >= L.height_src || col0 >= L.width_src)
+                continue;
+            const uint8_t *srow = L.src + b * L.src_bs + (size_t) r * L.width_src * 2;
+            uint32_t s[4];
+            fetch16((uintptr_t) srow + 2 * col0, (uintptr_t) srow + 2 * col0,
+                    (uintptr_t) srow + 2 * (col0 + 8 > L.width_src ? L.width_src : col0 + 8), s);
+            const uint16_t *l = L.map + (long) ((r * L.y_diff) >> 16) * L.luma_width;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                int j = col0 + k;
+                if (j < L.width_src) {
+                    uint32_t dp = (yuv[k >> 1] >> ((k & 1) * 16)) & 0xffff;
+                    uint32_t sp = (s[k >> 1] >> ((k & 1) * 16)) & 0xffff;
+                    uint32_t w = __ldg(l + ((j * L.x_diff) >> 16));
+                    uint32_t value = (uint32_t) mc_smoothstep((int32_t) w, (int32_t) (L.i_softness + w), L.step);
+                    uint32_t qy = ((sp & 0xff) * value + (dp & 0xff) * ((1u << 16) - value)) >> 16;
+                    uint32_t qc = ((sp >> 8) * value + (dp >> 8) * ((1u << 16) - value)) >> 16;
+                    uint32_t res = (qy & 0xff) | ((qc & 0xff) << 8);
+                    yuv[k >> 1] = (yuv[k >> 1] & ~(0xffffu << ((k & 1) * 16))) | (res << ((k & 1) * 16));
+                }
+            }
+        }
+    }
+
+    if (fmt == MLTCUDA_FMT_YUV422) {
+        *reinterpret_cast<uint4 *>(K.out + b * K.out_bs + pix0 * 2) = make_uint4(yuv[0], yuv[1], yuv[2], yuv[3]);
+        if (K.out_alpha)
+            *reinterpret_cast<uint2 *>(K.out_alpha + b * K.oa_bs + pix0) = make_uint2(al[0], al[1]);
+    } else {
+        uint8_t *p = K.out + b * K.out_bs + pix0 * 4;
+        reinterpret_cast<uint4 *>(p)[0] = make_uint4(rgba[0], rgba[1], rgba[2], rgba[3]);
+        reinterpret_cast<uint4 *>(p)[1] = make_uint4(rgba[4], rgba[5], rgba[6], rgba[7]);
+    }
+}
+
+} // namespace
+
+extern "C" int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!d || !d->in || !d->out, "null image pointer");
+    MC_BADARG(d->n_ops < 0 || d->n_ops > MLTCUDA_TRACTOR_MAX_OPS, "too many ops");
+    MC_BADARG(d->n_ops > 0 && !d->ops, "null op list");
+    if (d->width <= 0 || d->height <= 0)
+        return 0;
+    if (d->width % 8) {
+        mltcuda_set_error("fused tractor pass needs width %% 8 == 0 (got %d); run the ops unfused", d->width);
+        return MLTCUDA_E_UNSUPPORTED;
+    }
+    MC_BADARG(d->in_format != MLTCUDA_FMT_YUV422 && d->in_format != MLTCUDA_FMT_RGBA, "in_format must be yuv422 or rgba");
+    MC_BADARG(((uintptr_t) d->in | (uintptr_t) d->out | d->in_bstride | d->out_bstride) & 15, "frames must be 16-byte aligned");
+    MC_BADARG(((uintptr_t) d->in_alpha | (uintptr_t) d->out_alpha | d->in_alpha_bstride | d->out_alpha_bstride) & 7,
+              "alpha planes must be 8-byte aligned");
+    static thread_local TractorK K; // ~3 KB, passed by value as a __grid_constant__
+    K.width = d->width, K.height = d->height, K.in_format = d->in_format, K.n_ops = d->n_ops;
+    K.batch = d->batch > 0 ? d->batch : 1;
+    K.in = (const uint8_t *) d->in, K.in_alpha = d->in_alpha, K.out = (uint8_t *) d->out, K.out_alpha = d->out_alpha;
+    K.in_bs = d->in_bstride, K.ia_bs = d->in_alpha_bstride, K.out_bs = d->out_bstride, K.oa_bs = d->out_alpha_bstride;
+    if (K.batch > 1)
+        MC_BADARG(!K.in_bs || !K.out_bs, "batch > 1 needs in/out bstride");
+
+    int fmt = d->in_format, has_alpha = d->in_format == MLTCUDA_FMT_YUV422 && d->in_alpha != nullptr;
+    for (int i = 0; i < d->n_ops; i++) {
+        const mltcuda_tractor_op &o = d->ops[i];
+        TOp &t = K.ops[i];
+        t.kind = o.kind, t.to_format = o.to_format;
+        if (o.kind == MLTCUDA_TOP_COMPOSITE) {
+            MC_BADARG(fmt != MLTCUDA_FMT_YUV422, "composite op needs the running frame in yuv422");
+            mltcuda_composite_desc cd = o.u.composite;
+            MC_BADARG(!cd.src || cd.op < 0 || cd.op > 3, "bad composite op");
+            cd.alpha_a = has_alpha ? (uint8_t *) 1 : nullptr; // only its presence matters
+            mc_fill_composite_params(t.c.cp, &cd);
+            long off = (long) (cd.dest - (uint8_t *) d->out);
+            long rowb = (long) d->width * 2;
+            MC_BADARG(off < 0 || off >= rowb * d->height, "composite dest must point into `out`");
+            t.c.y = (int) (off / rowb), t.c.x = (int) ((off % rowb) / 2);
+            MC_BADARG(cd.stride_dest != rowb && cd.stride_dest != 2 * rowb, "composite stride_dest must be 1 or 2 rows");
+            t.c.row_step = (int) (cd.stride_dest / rowb);
+            t.c.rows = cd.rows;
+            t.c.src = cd.src, t.c.alpha_b = cd.alpha_b, t.c.luma = cd.luma;
+            t.c.stride_src = cd.stride_src, t.c.stride_ab = cd.stride_alpha_b;
+            t.c.src_bs = cd.src_bstride, t.c.ab_bs = cd.alpha_b_bstride, t.c.luma_bs = cd.luma_bstride;
+        } else if (o.kind == MLTCUDA_TOP_CONVERT) {
+            MC_BADARG(o.to_format != MLTCUDA_FMT_YUV422 && o.to_format != MLTCUDA_FMT_RGBA, "convert op: yuv422 or rgba");
+            MC_BADARG(o.to_format == fmt, "convert op to the current format");
+            fmt = o.to_format;
+            has_alpha = fmt == MLTCUDA_FMT_YUV422;
+        } else if (o.kind == MLTCUDA_TOP_AFFINE) {
+            MC_BADARG(fmt != MLTCUDA_FMT_RGBA || o.u.affine.format != MLTCUDA_FMT_RGBA, "affine op needs the running frame in rgba");
+            MC_BADARG(!o.u.affine.b_image, "null B image");
+            if (int e = mc_fill_affine_params(t.a.ap, &o.u.affine))
+                return e;
+            t.a.b_image = (const uint8_t *) o.u.affine.b_image, t.a.b_bs = o.u.affine.b_bstride;
+        } else if (o.kind == MLTCUDA_TOP_LUMA) {
+            const mltcuda_luma_desc &l = o.u.luma;
+            MC_BADARG(fmt != MLTCUDA_FMT_YUV422 || l.format != MLTCUDA_FMT_YUV422 || !l.map || l.field_order >= 0,
+                      "luma op: opaque progressive yuv422 wipe only");
+            MC_BADARG(l.width <= 0 || l.height <= 0 || !l.src, "bad luma op");
+            t.l.src = (const uint8_t *) l.src, t.l.map = l.map, t.l.luma_width = l.luma_width;
+            t.l.width_src = l.width_src > d->width ? d->width : l.width_src;
+            t.l.height_src = l.height_src > d->height ? d->height : l.height_src;
+            t.l.x_diff = (l.luma_width << 16) / l.width, t.l.y_diff = (l.luma_height << 16) / l.height;
+            t.l.i_softness = (uint32_t) (l.softness * (1 << 16));
+            float fpos = (l.pos + 0 * l.frame_delta * 0.5f) * (1.f + l.softness);
+            t.l.step = (uint32_t) ((1 << 16) * fpos);
+            t.l.src_bs = l.src_bstride;
+        } else {
+            mltcuda_set_error("unknown tractor op kind %d", o.kind);
+            return MLTCUDA_E_BADARG;
+        }
+    }
+    MC_BADARG(fmt != d->out_format, "out_format does not match the format the op list ends in");
+    long long total = (long long) (d->width / 8) * d->height * K.batch;
+    k_tractor<<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);
+    return mc_after_launch(ctx, "k_tractor");
+}

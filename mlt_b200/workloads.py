@@ -1,0 +1,114 @@
+"""Host-side parameter derivation for the benchmark configurations of BASELINE.json (cfg1..cfg4).
+
+This restates, for the concrete melt command lines of SURVEY 8(d), what the reference's host code
+computes per frame before it touches pixels -- composite_calculate / get_b_frame_image
+(src/modules/core/transition_composite.c:730-941) and the affine transition's get_image
+(src/modules/plus/transition_affine.c:414-729, get_affine :268-326, affine_* :93-210) -- as plain
+Python floats (= C doubles, same operation order).  The MLT module (mlt_b200/module) does the same
+through mlt_properties inside MLT; this file exists so bench.py and the tests can drive the C-ABI
+with exactly the per-frame parameters the reference would use (tests/test_cfg_vs_reference.py
+checks the derivation against frames rendered by the reference itself).
+"""
+import math
+
+W_UHD, H_UHD = 3840, 2160
+
+
+def rint(x):
+    return int(round(x))  # python round() is round-half-even like rint()
+
+
+def lerp_rect(k0, r0, k1, r1, pos):
+    """mlt_property_anim_get_rect, linear keyframes (src/framework/mlt_property.c:1265,1385-1389)."""
+    if pos <= k0:
+        return list(r0)
+    if pos >= k1:
+        return list(r1)
+    t = (pos - k0) / float(k1 - k0)
+    return [a + (b - a) * t for a, b in zip(r0, r1)]
+
+
+def composite_geometry(rect_pct, W, H, b_real_w, b_real_h):
+    """composite_calculate (:866-941) + get_b_frame_image default branch (:760-808) for
+    aligned=1, distort=0, fill=0, sar 1:1, geometry given in % with opacity fraction.
+    Returns (geometry dict for mltcuda_composite_setup, B width, B height)."""
+    x, y, w, h, o = rect_pct
+    item = dict(x=x * W, y=y * H, w=w * W, h=h * H, o=100.0 * min(o, 1.0))
+    nw, nh = W, H
+    norm_w, norm_h = int(item["w"]), int(item["h"])
+    sw, sh = b_real_w, b_real_h
+    if sw > norm_w:
+        sh = (sh * norm_w) // sw  # int arithmetic, :775
+        sw = norm_w
+    if sh > norm_h:
+        sw = (sw * norm_h) // sh
+        sh = norm_h
+    # alignment_calculate with halign = valign = 0 adds nothing
+    bw = rint(sw * W / nw)
+    bw -= bw % 2
+    bh = rint(sh * H / nh)
+    g = dict(item, nw=nw, nh=nh, sw=bw, sh=sh, x_src=0, y_src=0)  # :826-827 sw = *width
+    return g, bw, bh
+
+
+def mat_identity():
+    return [[1.0, 0.0, 0.0], [0.0, 1.0, 0.0], [0.0, 0.0, 1.0]]
+
+
+def mat_multiply(a, m):
+    """affine_multiply (:108-127): a <- a x m^T"""
+    return [[a[i][0] * m[j][0] + a[i][1] * m[j][1] + a[i][2] * m[j][2] for j in range(3)] for i in range(3)]
+
+
+def affine_params(W, H, rect_px, position, rotate_x_per_frame, b_w, b_h, interp="bilinear"):
+    """Per-frame sliced_desc of the affine transition (:616-714) for fill=1, distort=0, sar 1:1,
+    B requested at its native size, keyed=0, only rotate_x animated, no offsets/shear/alignment."""
+    x, y, w, h, o = rect_px
+    mix = 1.0 if o is None else min(o, 1.0)
+    geom_scale_x, geom_scale_y = b_w / w, b_h / h
+    d = dict(lower_x=-(x + w / 2.0), lower_y=-(y + h / 2.0), mix=mix, x_offset=b_w / 2.0, y_offset=b_h / 2.0,
+             b_alpha=0, minima=0.0, xmax=b_w - 1.0, ymax=b_h - 1.0, b_width=b_w, b_height=b_h)
+    m = mat_identity()
+    ang = 0.0 + rotate_x_per_frame * position
+    c, s = math.cos(ang * math.pi / 180), math.sin(ang * math.pi / 180)
+    m = mat_multiply(m, [[c, 0 - s, 0.0], [s, c, 0.0], [0.0, 0.0, 1.0]])  # affine_rotate_x
+    m = mat_multiply(m, [[1.0, 0.0, 0 - 0.0], [0.0, 1.0, 0.0], [0.0, 0.0, 1.0]])  # rotate_y(0)
+    m = mat_multiply(m, [[1.0, 0.0, 0.0], [0.0, 1.0, 0.0], [0.0, -0.0, 1.0]])  # rotate_z(0)
+    m = mat_multiply(m, [[1.0, 0.0, 0.0], [0.0, 1.0, 0.0], [0.0, 0.0, 1.0]])  # shear(0)
+    d["dz"] = m[2][2]
+    b_dar, consumer_dar = b_w / float(b_h), W / float(H)
+    if b_dar > consumer_dar:
+        sx, sy = geom_scale_x, geom_scale_x
+    else:
+        sx, sy = geom_scale_y, geom_scale_y
+    m = mat_multiply(m, [[sx, 0.0, 0.0], [0.0, sy, 0.0], [0.0, 0.0, 1.0]])  # affine_scale
+    d["matrix"] = m
+    if interp in ("nearest", "neighbor", "tiles", "fast_bilinear", None):
+        d["interp"], d["minima"], d["xmax"], d["ymax"] = 0, d["minima"] - 0.5, d["xmax"] + 0.49, d["ymax"] + 0.49
+    elif interp == "bilinear":
+        d["interp"] = 1
+    else:
+        d["interp"], d["minima"] = 2, d["minima"] - 1
+    return d
+
+
+# ---- the configurations ---------------------------------------------------------------------------
+
+CFG4 = dict(
+    name="cfg4_uhd_2160p_60_4track",
+    comp1=(0.05, 0.05, 0.40, 0.40, 0.80),
+    affine_k0=(0, (0.20, 0.20, 0.50, 0.50, 0.90)), affine_k1=(599, (0.30, 0.25, 0.60, 0.60, 0.70)),
+    rotate_x=0.5, colour=(0x30, 0x60, 0xc0, 0xa0),
+    comp2=(0.55, 0.55, 0.40, 0.40, 1.00),
+)
+
+
+def cfg4_frame(position, W=W_UHD, H=H_UHD, cfg=CFG4):
+    """Everything the three transitions of cfg4 need at timeline position `position`."""
+    g1, b1w, b1h = composite_geometry(cfg["comp1"], W, H, W, H)
+    g2, b2w, b2h = composite_geometry(cfg["comp2"], W, H, W, H)
+    (k0, r0), (k1, r1) = cfg["affine_k0"], cfg["affine_k1"]
+    r = lerp_rect(k0, r0, k1, r1, position)
+    rect_px = [r[0] * W, r[1] * H, r[2] * W, r[3] * H, r[4]]
+    aff = affine_params(W, H, rect_px, position, cfg["rotate_x"], W, H, "bilinear")
+    return dict(W=W, H=H, comp1=(g1, b1w, b1h), comp2=(g2, b2w, b2h), affine=aff)
