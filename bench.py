@@ -1,0 +1,375 @@
+#!/usr/bin/env python
+"""bench.py -- composited frames/s of BASELINE.json's cfg4 (4-track uhd_2160p_60 tractor:
+composite + affine + composite with the imageconvert yuv422<->rgba round trip per frame).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One "step" = FRAMES_PER_STEP consecutive timeline frames of the 4-track graph on one GPU, each
+frame one launch of the fused tractor kernel (mltcuda_tractor) with that frame's own keyframed
+parameters.  `value` = whole-job frames/s with the tracks resident in HBM (CUDA events on the
+launching stream); `e2e` = the same frames through the same C-ABI with HOST (pinned) track buffers:
+per frame H2D of the three noise tracks, the kernel, D2H of the composited frame, double-buffered
+on two streams.  The working set of a step (~1.6 GB) is >> the 126 MB L2, so no L2 flush is needed.
+N > 1: one process per GPU (torchrun), frames shard by rank, no collective on the data path
+(frames are independent); timing is the max over ranks after a barrier.
+--impl reference: the UNMODIFIED reference (oracle/_ref/bin/melt, built from /root/reference by
+oracle/Makefile.ref) renders the same graph on the host cores with real_time=-nproc.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np  # noqa: E402
+
+FRAMES_PER_STEP = 32
+W, H = 3840, 2160
+METRIC = "composited frames/sec, 4-track uhd_2160p_60 (composite+affine+composite+imageconvert)"
+
+MELT_CFG4 = ["noise:", "out={last}", "-track", "noise:", "out={last}", "-attach", "mirror:flip", "-transition",
+             "composite", "a_track=0", "b_track=1", "geometry=5%/5%:40%x40%:80%", "-track", "colour:0x3060c0a0",
+             "out={last}", "-transition", "affine", "a_track=0", "b_track=2",
+             "rect=0=20%/20%:50%x50%:90%; 599=30%/25%:60%x60%:70%", "rotate_x=0.5", "-track", "noise:", "out={last}",
+             "-transition", "composite", "a_track=0", "b_track=3", "geometry=55%/55%:40%x40%:100%"]
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+class Dist:
+    """barrier + max/sum over ranks; torch.distributed (gloo) only when launched under torchrun."""
+
+    def __init__(self):
+        self.rank, self.local_rank, self.world = dist_env()
+        self.pg = None
+        if self.world > 1:
+            import torch.distributed as dist
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("gloo", rank=self.rank, world_size=self.world)
+            self.pg = dist
+
+    def barrier(self):
+        if self.pg:
+            self.pg.barrier()
+
+    def reduce(self, x, op):
+        if not self.pg:
+            return x
+        import torch
+        t = torch.tensor([float(x)], dtype=torch.float64)
+        self.pg.all_reduce(t, op=getattr(self.pg.ReduceOp, op))
+        return float(t[0])
+
+    def close(self):
+        if self.pg:
+            self.pg.destroy_process_group()
+
+
+# ---- reference arm / CPU baseline ---------------------------------------------------------------
+
+def ref_env():
+    ref = os.path.join(ROOT, "oracle", "_ref")
+    e = dict(os.environ)
+    e["MLT_REPOSITORY"] = os.path.join(ref, "lib", "mlt")
+    e["MLT_DATA"] = os.path.join(ref, "share", "mlt")
+    e["MLT_PROFILES_PATH"] = os.path.join(ref, "share", "mlt", "profiles")
+    e["LD_LIBRARY_PATH"] = os.path.join(ref, "lib") + ":" + e.get("LD_LIBRARY_PATH", "")
+    return e, os.path.join(ref, "bin", "melt")
+
+
+def melt_cfg4_seconds(frames, threads):
+    """Wall time of the reference rendering `frames` frames of cfg4 (null consumer never drops)."""
+    env, melt = ref_env()
+    args = [a.format(last=frames - 1) for a in MELT_CFG4]
+    cmd = [melt, "-profile", "uhd_2160p_60"] + args + ["-consumer", "null", f"real_time=-{threads}", "-silent"]
+    t0 = time.perf_counter()
+    subprocess.run(cmd, env=env, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    return time.perf_counter() - t0
+
+
+def have_reference():
+    return os.path.exists(ref_env()[1])
+
+
+def cpu_port_fps(frames=2):
+    """Fallback CPU baseline: the plain-C oracle chain, 1 thread."""
+    import pipeline
+    inp = pipeline.inputs(0, W, H)
+    t0 = time.perf_counter()
+    for _ in range(frames):
+        pipeline.oracle_chain(inp)
+    return frames / (time.perf_counter() - t0)
+
+
+def run_reference(args, dist):
+    if dist.rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    sample_frames = 24
+    if have_reference():
+        kind = "reference"
+        for _ in range(args.warmup):
+            melt_cfg4_seconds(4, cores)
+        t = 0.0
+        for _ in range(args.steps):
+            t += melt_cfg4_seconds(sample_frames, cores)
+        fps = sample_frames * args.steps / t
+        ms = 1e3 * t / args.steps
+        sample = f"{sample_frames} frames of cfg4 per step through oracle/_ref/bin/melt -consumer null real_time=-{cores}"
+    else:
+        kind, cores = "port", 1
+        t0 = time.perf_counter()
+        fps = cpu_port_fps(max(1, args.steps))
+        ms = 1e3 * (time.perf_counter() - t0) / max(1, args.steps)
+        sample = "1 frame of cfg4 per step through the plain-C oracle chain (oracle/_ref not built)"
+    line = {"impl": "reference", "metric": METRIC, "value": round(fps, 3), "unit": "frames/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "cfg4_uhd_2160p_60_4track", "frames_per_step": sample_frames, "width": W, "height": H},
+            "cpu_baseline": {"value": round(fps, 3), "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": round(fps, 3), "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ---- clocks ----------------------------------------------------------------------------------------
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.th.join(timeout=2)
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx[0] if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+# ---- our arm ---------------------------------------------------------------------------------------
+
+def covered_pixels(aff):
+    """Destination pixels the affine op touches (dx,dy inside B), counted on a 2x2-subsampled grid."""
+    m = aff["matrix"]
+    xs = aff["lower_x"] + np.arange(0, W, 2, dtype=np.float64)
+    ys = aff["lower_y"] + np.arange(0, H, 2, dtype=np.float64)
+    X, Y = np.meshgrid(xs, ys)
+    dx = (m[0][0] * X + m[0][1] * Y + m[0][2]) / aff["dz"] + aff["x_offset"]
+    dy = (m[1][0] * X + m[1][1] * Y + m[1][2]) / aff["dz"] + aff["y_offset"]
+    inside = (dx >= aff["minima"]) & (dx <= aff["xmax"]) & (dy >= aff["minima"]) & (dy <= aff["ymax"])
+    return int(inside.sum()) * 4
+
+
+def run_ours(args, dist):
+    import pipeline
+    from mlt_b200 import Context, abi, workloads
+    lib = abi.load()
+    ndev = lib.mltcuda_device_count()
+    if ndev <= 0:
+        raise SystemExit("bench.py: no CUDA device visible; the product path has no CPU fallback")
+    dev = dist.local_rank % ndev
+    ctx = Context(dev)
+    ctx2 = Context(dev)  # second stream for the double-buffered end-to-end leg
+    F = FRAMES_PER_STEP
+    first = dist.rank * F  # each rank renders its own slice of the timeline
+    frames = [workloads.cfg4_frame(first + i, W, H) for i in range(F)]
+    (g1, b1w, b1h), (g2, b2w, b2h) = frames[0]["comp1"], frames[0]["comp2"]
+    fb, b1b, b3b = W * H * 2, b1w * b1h * 2, b2w * b2h * 2
+
+    # resident tracks: device-side noise producers (bit-exact with producer_noise.c), flipped track 1
+    # uploaded from the oracle-free host path below
+    d_in, d_b1, d_b3 = ctx.alloc(F * fb), ctx.alloc(F * b1b), ctx.alloc(F * b3b)
+    d_bc, d_bcy, d_bca = ctx.alloc(W * H * 4), ctx.alloc(fb), ctx.alloc(W * H)
+    d_out, d_alpha = ctx.alloc(F * fb), ctx.alloc(F * W * H)
+    abi.check(lib.mltcuda_noise(ctx.h, d_in.ptr, W, H, first, F, fb), "noise")
+    abi.check(lib.mltcuda_noise(ctx.h, d_b3.ptr, b2w, b2h, first, F, b3b), "noise")
+    abi.check(lib.mltcuda_noise(ctx.h, d_b1.ptr, b1w, b1h, first + 100000, F, b1b), "noise")  # decorrelated track 1
+    r, g, b, a = workloads.CFG4["colour"]
+    abi.check(lib.mltcuda_colour(ctx.h, d_bcy.ptr, d_bca.ptr, 3, W, H, r, g, b, a), "colour")
+    ctx.call("mltcuda_convert", abi.ConvertDesc(src_format=3, dst_format=2, width=W, height=H, src=d_bcy.ptr,
+                                                dst=d_bc.ptr, src_alpha=d_bca.ptr, batch=1))
+    ctx.sync()
+
+    descs = [pipeline.tractor_desc(ctx, frames[i], d_in.at(i * fb), d_out.at(i * fb), d_alpha.at(i * W * H),
+                                   d_b1.at(i * b1b), d_bc.ptr, d_b3.at(i * b3b)) for i in range(F)]
+
+    def step():
+        for d in descs:
+            rc = lib.mltcuda_tractor(ctx.h, C.byref(d))
+            if rc:
+                abi.check(rc, "mltcuda_tractor")
+
+    ev0, ev1 = lib.mltcuda_event_create(), lib.mltcuda_event_create()
+    for _ in range(args.warmup):
+        step()
+    ctx.sync()
+    clocks = ClockSampler(dev)
+    clocks.start()
+    dist.barrier()
+    l0 = ctx.launches()
+    lib.mltcuda_event_record(ctx.h, ev0)
+    for _ in range(args.steps):
+        step()
+    lib.mltcuda_event_record(ctx.h, ev1)
+    ctx.sync()
+    dist.barrier()
+    ms = lib.mltcuda_event_elapsed_ms(ev0, ev1)
+    launches = ctx.launches() - l0
+    clk = clocks.stop()
+    ms_max = dist.reduce(ms, "MAX")
+    total_launches = int(dist.reduce(launches, "SUM"))
+    value = dist.world * F * args.steps / (ms_max / 1e3)
+
+    # roofline of the dominant (only) kernel: algorithmic bytes per launch / average launch time
+    cov = [covered_pixels(f["affine"]) for f in frames]
+    alg = [W * H * (2 + 2 + 1) + b1b + b3b + 4 * c for c in cov]  # A r2 + out w2 + alpha w1, layers once, 4 B/covered px
+    alg_per_launch = float(np.mean(alg))
+    avg_launch_s = (ms / 1e3) / max(launches, 1)
+    achieved = alg_per_launch / avg_launch_s / 1e9
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    roofline = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                "frac": round(achieved / peak, 4), "traffic": None, "kernel": "k_tractor",
+                "algorithmic_bytes_per_launch": int(alg_per_launch),
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s"}
+
+    # ---- end to end: host (pinned) tracks in, composited frame out, two streams -------------------
+    def pinned(nbytes):
+        p = lib.mltcuda_host_alloc(nbytes)
+        if not p:
+            raise SystemExit("pinned alloc failed")
+        return p
+
+    h_in, h_b1, h_b3, h_out = pinned(F * fb), pinned(F * b1b), pinned(F * b3b), pinned(2 * fb)
+    abi.check(lib.mltcuda_download(ctx.h, h_in, d_in.ptr, F * fb))
+    abi.check(lib.mltcuda_download(ctx.h, h_b1, d_b1.ptr, F * b1b))
+    abi.check(lib.mltcuda_download(ctx.h, h_b3, d_b3.ptr, F * b3b))
+    ctx.sync()
+    slots = []
+    for s, c in enumerate((ctx, ctx2)):
+        sl = dict(ctx=c, d_in=c.alloc(fb), d_b1=c.alloc(b1b), d_b3=c.alloc(b3b), d_out=c.alloc(fb), d_al=c.alloc(W * H),
+                  done=lib.mltcuda_event_create(), used=False, h_out=h_out + s * fb)
+        slots.append(sl)
+    e2e_descs = [[pipeline.tractor_desc(sl["ctx"], frames[i], sl["d_in"].ptr, sl["d_out"].ptr, sl["d_al"].ptr,
+                                        sl["d_b1"].ptr, d_bc.ptr, sl["d_b3"].ptr) for i in range(F)] for sl in slots]
+
+    def e2e_step():
+        for i in range(F):
+            s = i & 1
+            sl = slots[s]
+            c = sl["ctx"]
+            if sl["used"]:
+                lib.mltcuda_event_sync(sl["done"])  # the consumer has taken the previous frame of this slot
+            lib.mltcuda_upload(c.h, sl["d_in"].ptr, h_in + i * fb, fb)
+            lib.mltcuda_upload(c.h, sl["d_b1"].ptr, h_b1 + i * b1b, b1b)
+            lib.mltcuda_upload(c.h, sl["d_b3"].ptr, h_b3 + i * b3b, b3b)
+            rc = lib.mltcuda_tractor(c.h, C.byref(e2e_descs[s][i]))
+            if rc:
+                abi.check(rc, "mltcuda_tractor")
+            lib.mltcuda_download(c.h, sl["h_out"], sl["d_out"].ptr, fb)
+            lib.mltcuda_event_record(c.h, sl["done"])
+            sl["used"] = True
+
+    e2e_steps = max(1, min(args.steps, 5))
+    e2e_step()
+    ctx.sync(), ctx2.sync()
+    dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    ctx.sync(), ctx2.sync()
+    e2e_s = time.perf_counter() - t0
+    dist.barrier()
+    e2e_max = dist.reduce(e2e_s, "MAX")
+    e2e_val = dist.world * F * e2e_steps / e2e_max
+    # the end-to-end result is the frame the device-resident leg produced
+    out_host = np.ctypeslib.as_array(C.cast(h_out, C.POINTER(C.c_uint8)), shape=(2, fb))
+    ref_out = ctx.get(d_out, (fb,), offset=(F - 1) * fb)
+    e2e_ok = bool(np.array_equal(out_host[(F - 1) & 1], ref_out))
+
+    cpu = None
+    if dist.rank == 0 and dist.world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        if have_reference():
+            melt_cfg4_seconds(4, cores)
+            n = 48
+            t = melt_cfg4_seconds(n, cores)
+            cpu = {"value": round(n / t, 3), "unit": "frames/s", "cores": cores, "kind": "reference",
+                   "sample": f"{n} frames of cfg4 through oracle/_ref/bin/melt -consumer null real_time=-{cores} "
+                             f"({t:.1f} s wall, incl. the CPU noise producers)"}
+        else:
+            cpu = {"value": round(cpu_port_fps(2), 3), "unit": "frames/s", "cores": 1, "kind": "port",
+                   "sample": "2 frames of cfg4 through the plain-C oracle chain"}
+
+    if dist.rank == 0:
+        line = {"metric": METRIC, "value": round(value, 1), "unit": "frames/s", "n_gpus": dist.world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_max / args.steps, 4),
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": {"workload": "cfg4_uhd_2160p_60_4track", "frames_per_step": F, "width": W, "height": H,
+                           "launches_per_frame": 1, "l2": "inputs larger than L2 (step working set ~1.6 GB)",
+                           "parallelism": f"frame-sharded x{dist.world}, no collective"},
+                "e2e": {"value": round(e2e_val, 1), "unit": "frames/s", "h2d_bytes_per_step": F * (fb + b1b + b3b),
+                        "d2h_bytes_per_step": F * fb, "steps": e2e_steps, "matches_device_leg": e2e_ok},
+                "gpu_launches": total_launches, "roofline": roofline, "clocks": clk}
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    ctx2.close()
+    ctx.close()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    dist = Dist()
+    try:
+        if args.impl == "reference":
+            run_reference(args, dist)
+        else:
+            run_ours(args, dist)
+    finally:
+        dist.close()
+
+
+if __name__ == "__main__":
+    main()

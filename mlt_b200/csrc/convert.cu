@@ -176,10 +176,13 @@ template <int CELL> __global__ void __launch_bounds__(256) k_convert_pair(CvtPar
             const uint8_t *pv = src + (size_t) w * h + (size_t) (w / 2) * (h / 2) + ((w / 2) * line) / 2 + pi;
             yw = py[0] | (pu[0] << 8) | (py[1] << 16) | (pv[0] << 24);
         } else {
-            yw = *reinterpret_cast<const uint32_t *>(src + line * P.src_stride + 4 * (size_t) pi);
+            // rows of odd-width yuv422 images are only 2-byte aligned
+            const uint16_t *s16 = reinterpret_cast<const uint16_t *>(src + line * P.src_stride + 4 * (size_t) pi);
+            yw = (uint32_t) s16[0] | ((uint32_t) s16[1] << 16);
         }
         if (CELL == C_420_422) {
-            *reinterpret_cast<uint32_t *>(dst + line * P.dst_stride + 4 * (size_t) pi) = yw;
+            uint16_t *d16 = reinterpret_cast<uint16_t *>(dst + line * P.dst_stride + 4 * (size_t) pi);
+            d16[0] = (uint16_t) yw, d16[1] = (uint16_t) (yw >> 16);
             return;
         }
         uint32_t a0 = sa ? sa[0] : 0xff, a1 = sa ? sa[1] : 0xff, p0, p1;
@@ -225,7 +228,8 @@ template <int CELL> __global__ void __launch_bounds__(256) k_convert_pair(CvtPar
             mc_rgb2yuv(p[0] & 0xff, (p[0] >> 8) & 0xff, (p[0] >> 16) & 0xff, y0, u0, v0);
             d[0] = y0, d[1] = u0;
         } else {
-            *reinterpret_cast<uint32_t *>(d) = mc_rgba2_to_yuyv(p[0], p[1]);
+            uint32_t yw = mc_rgba2_to_yuyv(p[0], p[1]);
+            reinterpret_cast<uint16_t *>(d)[0] = (uint16_t) yw, reinterpret_cast<uint16_t *>(d)[1] = (uint16_t) (yw >> 16);
         }
         return;
     }

@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(256) k_rescale_yuv422(uint8_t *dst, int ow, in
     r |= (uint32_t) in_line[base] << 16;
     base &= 0xfffffffc;
     r |= (uint32_t) in_line[base + 3] << 24;
-    *reinterpret_cast<uint32_t *>(o) = r;
+    reinterpret_cast<uint16_t *>(o)[0] = (uint16_t) r, reinterpret_cast<uint16_t *>(o)[1] = (uint16_t) (r >> 16);
 }
 
 int ensure_noise_tab(mltcuda_ctx *ctx)
