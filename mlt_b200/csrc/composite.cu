@@ -80,24 +80,8 @@ __global__ void __launch_bounds__(256) k_composite_rows(CompK K)
         fetch16(lrow + 2 * (long) j0, lrow + 2 * (long) jlo, lrow + 2 * (long) jhi, lum);
     }
 
-    uint32_t o[4], oa[2] = {0, 0};
-#pragma unroll
-    for (int k = 0; k < 8; k++) {
-        uint32_t dp = (d[k >> 1] >> ((k & 1) * 16)) & 0xffff;
-        uint32_t sp = (s[k >> 1] >> ((k & 1) * 16)) & 0xffff;
-        uint32_t abk = (ab[k >> 2] >> ((k & 3) * 8)) & 0xff;
-        uint32_t aak = (aa[k >> 2] >> ((k & 3) * 8)) & 0xff;
-        uint32_t lk = (lum[k >> 1] >> ((k & 1) * 16)) & 0xffff;
-        int j = j0 + k;
-        uint32_t res = dp;
-        if (j >= jlo && j < jhi)
-            res = mc_composite_px(P, j, dp, sp, abk, aak, lk);
-        if (k & 1)
-            o[k >> 1] |= res << 16;
-        else
-            o[k >> 1] = res;
-        oa[k >> 2] |= aak << ((k & 3) * 8);
-    }
+    mc_composite_group8(P, j0, jlo, jhi, d, s, ab, aa, lum);
+    const uint32_t *o = d, *oa = aa;
     if (jlo == j0 && jhi == j0 + 8) {
         *dptr = make_uint4(o[0], o[1], o[2], o[3]);
     } else {

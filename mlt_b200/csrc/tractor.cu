@@ -57,7 +57,10 @@ struct TractorK
     TOp ops[MLTCUDA_TRACTOR_MAX_OPS];
 };
 
-__global__ void __launch_bounds__(256) k_tractor(const __grid_constant__ TractorK K)
+// ONLY_BL: every affine op of the list samples bilinearly (the default "consumer.rescale"), so the
+// nearest / bicubic samplers are compiled out -- they would otherwise set the register budget.
+template <bool ONLY_BL>
+__global__ void __launch_bounds__(256, ONLY_BL ? 3 : 1) k_tractor(const __grid_constant__ TractorK K)
 {
     const int cpr = K.width >> 3;
     long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
@@ -111,27 +114,10 @@ __global__ void __launch_bounds__(256) k_tractor(const __grid_constant__ Tractor
                 uintptr_t lrow = (uintptr_t) (C.luma + b * (C.luma_bs / 2) + rr * C.stride_ab);
                 fetch16(lrow + 2 * (long) j0, lrow + 2 * (long) jlo, lrow + 2 * (long) jhi, lum);
             }
-            uint32_t o[4], oa[2] = {0, 0};
-#pragma unroll
-            for (int k = 0; k < 8; k++) {
-                uint32_t dp = (yuv[k >> 1] >> ((k & 1) * 16)) & 0xffff;
-                uint32_t sp = (s[k >> 1] >> ((k & 1) * 16)) & 0xffff;
-                uint32_t abk = (ab[k >> 2] >> ((k & 3) * 8)) & 0xff;
-                uint32_t aak = (al[k >> 2] >> ((k & 3) * 8)) & 0xff;
-                uint32_t lk = (lum[k >> 1] >> ((k & 1) * 16)) & 0xffff;
-                int j = j0 + k;
-                uint32_t res = dp;
-                if (j >= jlo && j < jhi)
-                    res = mc_composite_px(C.cp, j, dp, sp, abk, aak, lk);
-                if (k & 1)
-                    o[k >> 1] |= res << 16;
-                else
-                    o[k >> 1] = res;
-                oa[k >> 2] |= aak << ((k & 3) * 8);
-            }
-            yuv[0] = o[0], yuv[1] = o[1], yuv[2] = o[2], yuv[3] = o[3];
+            uint32_t na[2] = {al[0], al[1]};
+            mc_composite_group8(C.cp, j0, jlo, jhi, yuv, s, ab, na, lum);
             if (has_alpha)
-                al[0] = oa[0], al[1] = oa[1];
+                al[0] = na[0], al[1] = na[1];
         } else if (op.kind == MLTCUDA_TOP_CONVERT) {
             if (op.to_format == MLTCUDA_FMT_RGBA) { // filter_imageconvert.c:58-111
 #pragma unroll
@@ -145,17 +131,25 @@ __global__ void __launch_bounds__(256) k_tractor(const __grid_constant__ Tractor
 #pragma unroll
                 for (int k = 0; k < 4; k++)
                     yuv[k] = mc_rgba2_to_yuyv(rgba[2 * k], rgba[2 * k + 1]);
-                al[0] = (rgba[0] >> 24) | ((rgba[1] >> 24) << 8) | ((rgba[2] >> 24) << 16) | ((rgba[3] >> 24) << 24);
-                al[1] = (rgba[4] >> 24) | ((rgba[5] >> 24) << 8) | ((rgba[6] >> 24) << 16) | ((rgba[7] >> 24) << 24);
+                al[0] = __byte_perm(__byte_perm(rgba[0], rgba[1], 0x0073), __byte_perm(rgba[2], rgba[3], 0x0073), 0x5410);
+                al[1] = __byte_perm(__byte_perm(rgba[4], rgba[5], 0x0073), __byte_perm(rgba[6], rgba[7], 0x0073), 0x5410);
                 fmt = MLTCUDA_FMT_YUV422, has_alpha = 1;
             }
         } else if (op.kind == MLTCUDA_TOP_AFFINE) {
+            const AffineParams &P = op.a.ap;
+            const AffineRow R = mc_affine_row(P, r);
+            if (mc_affine_reject(P, R, col0, 8))
+                continue;
             const uint8_t *bimg = op.a.b_image + b * op.a.b_bs;
 #pragma unroll
             for (int k = 0; k < 8; k++) {
-                uint32_t d[4] = {rgba[k] & 0xff, (rgba[k] >> 8) & 0xff, (rgba[k] >> 16) & 0xff, rgba[k] >> 24};
-                if (mc_affine_px<uint8_t>(op.a.ap, bimg, col0 + k, r, d))
+                double dx, dy;
+                mc_affine_map(P, R, col0 + k, dx, dy);
+                if (mc_affine_inside(P, dx, dy)) {
+                    uint32_t d[4] = {rgba[k] & 0xff, (rgba[k] >> 8) & 0xff, (rgba[k] >> 16) & 0xff, rgba[k] >> 24};
+                    mc_affine_sample<uint8_t, ONLY_BL ? 1 : -1>(P, bimg, dx, dy, d);
                     rgba[k] = d[0] | (d[1] << 8) | (d[2] << 16) | (d[3] << 24);
+                }
             }
         } else if (op.kind == MLTCUDA_TOP_LUMA) { // transition_luma.c:452-463, progressive
             const TLumaOp &L = op.l;
@@ -222,6 +216,7 @@ extern "C" int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d)
         MC_BADARG(!K.in_bs || !K.out_bs, "batch > 1 needs in/out bstride");
 
     int fmt = d->in_format, has_alpha = d->in_format == MLTCUDA_FMT_YUV422 && d->in_alpha != nullptr;
+    bool only_bl = true;
     for (int i = 0; i < d->n_ops; i++) {
         const mltcuda_tractor_op &o = d->ops[i];
         TOp &t = K.ops[i];
@@ -253,6 +248,7 @@ extern "C" int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d)
             if (int e = mc_fill_affine_params(t.a.ap, &o.u.affine))
                 return e;
             t.a.b_image = (const uint8_t *) o.u.affine.b_image, t.a.b_bs = o.u.affine.b_bstride;
+            only_bl = only_bl && t.a.ap.interp == MLTCUDA_INTERP_BL;
         } else if (o.kind == MLTCUDA_TOP_LUMA) {
             const mltcuda_luma_desc &l = o.u.luma;
             MC_BADARG(fmt != MLTCUDA_FMT_YUV422 || l.format != MLTCUDA_FMT_YUV422 || !l.map || l.field_order >= 0,
@@ -273,6 +269,9 @@ extern "C" int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d)
     }
     MC_BADARG(fmt != d->out_format, "out_format does not match the format the op list ends in");
     long long total = (long long) (d->width / 8) * d->height * K.batch;
-    k_tractor<<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);
+    if (only_bl)
+        k_tractor<true><<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);
+    else
+        k_tractor<false><<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);
     return mc_after_launch(ctx, "k_tractor");
 }
