@@ -42,10 +42,8 @@ template <typename T> __global__ void __launch_bounds__(256) k_affine(AffK K)
         int ii = i, jj = j;
 #pragma unroll
         for (int k = 0; k < PPT; k++) {
-            double x = P.lower_x + (double) jj, y = P.lower_y + (double) ii;
-            dxs[k] = (P.m00 * x + P.m01 * y + P.m02) / P.dz + P.x_offset;
-            dys[k] = (P.m10 * x + P.m11 * y + P.m12) / P.dz + P.y_offset;
-            bool in = p0 + k < npx && dxs[k] >= P.minima && dxs[k] <= P.xmax && dys[k] >= P.minima && dys[k] <= P.ymax;
+            mc_affine_map(P, mc_affine_row(P, ii), jj, dxs[k], dys[k]);
+            bool in = p0 + k < npx && mc_affine_inside(P, dxs[k], dys[k]);
             hit |= in ? (1 << k) : 0;
             if (++jj == K.a_width)
                 jj = 0, ii++;
@@ -108,6 +106,68 @@ template <typename T> __global__ void __launch_bounds__(256) k_affine(AffK K)
     }
 }
 
+
+// Row-aligned fast path (a_width % PPT == 0, the usual case): 2-D blocks of 32 groups x 8 rows so a
+// CTA's B taps share L1 lines across rows; whole groups are rejected from their two end pixels
+// (mc_affine_reject) before any A traffic; INTERP is a template parameter so only one sampler is
+// compiled into each instantiation.
+template <typename T, int INTERP> __global__ void __launch_bounds__(256) k_affine_rows(AffK K)
+{
+    constexpr int PPT = sizeof(T) == 1 ? 4 : 2;
+    const int g = blockIdx.x * 32 + threadIdx.x;
+    const int i = blockIdx.y * 8 + threadIdx.y;
+    const int j = g * PPT;
+    if (j >= K.a_width || i >= K.a_height)
+        return;
+    const int b = blockIdx.z;
+    const AffineParams &P = K.p;
+    const AffineRow R = mc_affine_row(P, i);
+    if (mc_affine_reject(P, R, j, PPT))
+        return;
+    double dxs[PPT], dys[PPT];
+    int hit = 0;
+#pragma unroll
+    for (int k = 0; k < PPT; k++) {
+        mc_affine_map(P, R, j + k, dxs[k], dys[k]);
+        hit |= mc_affine_inside(P, dxs[k], dys[k]) ? (1 << k) : 0;
+    }
+    if (!hit)
+        return;
+    T *q = reinterpret_cast<T *>(K.a_image + b * K.a_bs) + ((size_t) i * K.a_width + j) * 4;
+    const T *bimg = reinterpret_cast<const T *>(K.b_image + b * K.b_bs);
+    uint4 a = ld16(q);
+    uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int k = 0; k < PPT; k++) {
+        if (hit & (1 << k)) {
+            uint32_t d[4];
+            if (sizeof(T) == 1) {
+                d[0] = aw[k] & 0xff, d[1] = (aw[k] >> 8) & 0xff, d[2] = (aw[k] >> 16) & 0xff, d[3] = aw[k] >> 24;
+            } else {
+                d[0] = aw[2 * k] & 0xffff, d[1] = aw[2 * k] >> 16, d[2] = aw[2 * k + 1] & 0xffff, d[3] = aw[2 * k + 1] >> 16;
+            }
+            mc_affine_sample<T, INTERP>(P, bimg, dxs[k], dys[k], d);
+            if (sizeof(T) == 1)
+                aw[k] = d[0] | (d[1] << 8) | (d[2] << 16) | (d[3] << 24);
+            else
+                aw[2 * k] = d[0] | (d[1] << 16), aw[2 * k + 1] = d[2] | (d[3] << 16);
+        }
+    }
+    *reinterpret_cast<uint4 *>(q) = make_uint4(aw[0], aw[1], aw[2], aw[3]);
+}
+
+template <typename T> static void launch_affine_rows(const AffK &K, int interp, cudaStream_t st)
+{
+    constexpr int PPT = sizeof(T) == 1 ? 4 : 2;
+    dim3 blk(32, 8, 1), grd((K.a_width / PPT + 31) / 32, (K.a_height + 7) / 8, K.batch);
+    if (interp == MLTCUDA_INTERP_BL)
+        k_affine_rows<T, 1><<<grd, blk, 0, st>>>(K);
+    else if (interp == MLTCUDA_INTERP_NN)
+        k_affine_rows<T, 0><<<grd, blk, 0, st>>>(K);
+    else
+        k_affine_rows<T, 2><<<grd, blk, 0, st>>>(K);
+}
+
 } // namespace
 
 int mc_fill_affine_params(AffineParams &p, const mltcuda_affine_desc *d)
@@ -149,7 +209,13 @@ extern "C" int mltcuda_affine(mltcuda_ctx *ctx, const mltcuda_affine_desc *d)
         MC_BADARG(!K.a_bs, "batch > 1 needs a_bstride");
     const int ppt = d->format == MLTCUDA_FMT_RGBA ? 4 : 2;
     long long total = (((long long) d->a_width * d->a_height + ppt - 1) / ppt) * K.batch;
-    if (d->format == MLTCUDA_FMT_RGBA)
+    const bool rows_ok = d->a_width % ppt == 0 && ((uintptr_t) d->a_image & 15) == 0 && (K.a_bs & 15) == 0
+                         && (d->a_height + 7) / 8 <= 65535 && K.batch <= 65535;
+    if (rows_ok && d->format == MLTCUDA_FMT_RGBA)
+        launch_affine_rows<uint8_t>(K, d->interp, ctx->stream);
+    else if (rows_ok)
+        launch_affine_rows<uint16_t>(K, d->interp, ctx->stream);
+    else if (d->format == MLTCUDA_FMT_RGBA)
         k_affine<uint8_t><<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);
     else
         k_affine<uint16_t><<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);

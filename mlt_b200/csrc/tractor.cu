@@ -60,17 +60,14 @@ struct TractorK
 // ONLY_BL: every affine op of the list samples bilinearly (the default "consumer.rescale"), so the
 // nearest / bicubic samplers are compiled out -- they would otherwise set the register budget.
 template <bool ONLY_BL>
-__global__ void __launch_bounds__(256, ONLY_BL ? 3 : 1) k_tractor(const __grid_constant__ TractorK K)
+__global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_constant__ TractorK K)
 {
-    const int cpr = K.width >> 3;
-    long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
-    long long total = (long long) cpr * K.height * K.batch;
-    if (gid >= total)
+    // 2-D CTA: 32 groups (256 px) x 8 rows -- no div/mod, and the B taps of neighbouring rows share L1
+    const int c = blockIdx.x * 32 + threadIdx.x;
+    const int r = blockIdx.y * 8 + threadIdx.y;
+    if (c >= (K.width >> 3) || r >= K.height)
         return;
-    const int c = (int) (gid % cpr);
-    long long t = gid / cpr;
-    const int r = (int) (t % K.height);
-    const int b = (int) (t / K.height);
+    const int b = blockIdx.z;
     const int col0 = c * 8;
     const size_t pix0 = (size_t) r * K.width + col0;
 
@@ -268,10 +265,11 @@ extern "C" int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d)
         }
     }
     MC_BADARG(fmt != d->out_format, "out_format does not match the format the op list ends in");
-    long long total = (long long) (d->width / 8) * d->height * K.batch;
+    MC_BADARG((d->height + 7) / 8 > 65535 || K.batch > 65535, "frame too tall / batch too large for one launch");
+    dim3 blk(32, 8, 1), grd((d->width / 8 + 31) / 32, (d->height + 7) / 8, K.batch);
     if (only_bl)
-        k_tractor<true><<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);
+        k_tractor<true><<<grd, blk, 0, ctx->stream>>>(K);
     else
-        k_tractor<false><<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);
+        k_tractor<false><<<grd, blk, 0, ctx->stream>>>(K);
     return mc_after_launch(ctx, "k_tractor");
 }
