@@ -1,0 +1,83 @@
+/*
+ * cuda_module.h -- shared declarations of the MLT "cuda" module (libmltcuda.so).
+ *
+ * The module is the host side (plain C, links libmlt-7) of the B200 compositing path: it registers
+ * the services `composite`, `luma`, `affine` (transitions) and `imageconvert` (filter) under the
+ * reference's names and properties, and runs their pixel work through the C-ABI of
+ * include/mltcuda.h (libmltcuda_rt.so).  There is no CPU pixel path in this module.
+ *
+ * Device residency protocol (precedent: src/modules/placebo/gpu_context.c:403-447 in the
+ * reference): a frame whose pixels live in HBM carries format mlt_image_private, the image pointer
+ * is a `cuda_image` handle owned by the frame (destructor frees the device buffers) and the frame
+ * property "mlt_image_private" is the string "cuda".  A CUDA service that pulls an input raises the
+ * frame's "_cuda_requested" counter around mlt_frame_get_image(); while it is raised the module's
+ * converter (prepended to the frame's convert chain) leaves private images alone and turns host
+ * images into private ones, so chained CUDA services never round-trip through host memory.  When
+ * the counter is zero (a CPU filter or the consumer is asking) the converter downloads.
+ */
+#ifndef MLT_CUDA_MODULE_H
+#define MLT_CUDA_MODULE_H
+
+#include <framework/mlt.h>
+#include <framework/mlt_luma_map.h>
+#include <stdint.h>
+
+#include "mltcuda.h"
+
+#define CUDA_IMAGE_MAGIC 0x43554441u /* "CUDA" */
+#define CUDA_IMAGE_TAG "mlt_image_private"
+#define CUDA_IMAGE_TAG_VALUE "cuda"
+#define CUDA_REQUESTED "_cuda_requested"
+
+typedef struct cuda_image_s
+{
+    uint32_t magic;
+    mltcuda_ctx *ctx;      /* context (GPU + stream + pool) the buffers belong to */
+    mlt_image_format format; /* pixel format of `data`: rgb, rgba, yuv422, yuv420p, rgba64 */
+    int width, height;
+    void *data;            /* device */
+    uint8_t *alpha;        /* device, 1 B/px, or NULL */
+} *cuda_image;
+
+/* --- runtime (cuda_image.c) -------------------------------------------------------------- */
+
+/* The calling thread's context; created on first use, worker k -> GPU k mod G.
+ * NULL (and an error logged) when no device is usable: callers then fail their get_image. */
+mltcuda_ctx *cuda_thread_ctx(void);
+
+size_t cuda_format_bytes(mlt_image_format format, int width, int height);
+int cuda_format_supported(mlt_image_format format);
+
+cuda_image cuda_image_new(mltcuda_ctx *ctx, mlt_image_format format, int width, int height, int with_alpha);
+void cuda_image_close(cuda_image ci);
+int cuda_image_ensure_alpha(cuda_image ci, int fill); /* allocates + memsets if missing */
+void cuda_image_drop_alpha(cuda_image ci);
+
+/* Is the frame's current image one of ours? */
+cuda_image cuda_frame_peek(mlt_frame frame, uint8_t *image, mlt_image_format format);
+/* Install `ci` as the frame's image (frame takes ownership). */
+int cuda_frame_set_image(mlt_frame frame, cuda_image ci);
+
+/* Pull the frame's image as a device image in `format` (yuv422 / rgba / rgba64) at the requested
+ * size (in/out like mlt_frame_get_image).  Uploads / converts on the device as needed.  The
+ * returned handle stays owned by the frame.  NULL on error. */
+cuda_image cuda_frame_get_image(mlt_frame frame, mlt_image_format format, int *width, int *height, int writable);
+
+/* Convert a device image to another format on the device (imageconvert matrix).  Returns a NEW
+ * image (caller owns) or NULL if the cell does not exist / on error. */
+cuda_image cuda_image_convert(cuda_image src, mlt_image_format to);
+
+/* The converter callback (mlt_convert_image) the services prepend to frames. */
+int cuda_convert_image(mlt_frame frame, uint8_t **image, mlt_image_format *format, mlt_image_format output);
+
+/* Device copy of a host uint16 luma map, cached on `owner` under `key` until the host pointer or
+ * the size changes. */
+uint16_t *cuda_cached_map(mlt_properties owner, const char *key, mltcuda_ctx *ctx, const uint16_t *host, int w, int h);
+
+/* --- constructors (one file per service) ---------------------------------------------------- */
+mlt_transition cuda_transition_composite_init(mlt_profile, mlt_service_type, const char *, char *);
+mlt_transition cuda_transition_luma_init(mlt_profile, mlt_service_type, const char *, char *);
+mlt_transition cuda_transition_affine_init(mlt_profile, mlt_service_type, const char *, char *);
+mlt_filter cuda_filter_imageconvert_init(mlt_profile, mlt_service_type, const char *, char *);
+
+#endif

@@ -1,0 +1,105 @@
+/*
+ * factory.c (cuda module) -- mlt_register for libmltcuda.so.
+ *
+ * Registers the four services of the compositing hot path under the reference's names
+ * (`composite`, `luma`, `affine` transitions: src/modules/core/factory.c:234-236,
+ * src/modules/plus/factory.c:190; `imageconvert` filter: core/factory.c:231) and under `cuda.*`
+ * aliases so both implementations can be instantiated side by side.
+ *
+ * Deterministic override: the repository loads modules in readdir order and a duplicate name
+ * simply overwrites (src/framework/mlt_repository.c:79,263-276), so registration alone cannot
+ * guarantee which `composite` wins.  The module therefore also listens to the factory's
+ * "transition-create-request" / "filter-create-request" events (src/framework/mlt_factory.c:
+ * 370-388,425-443): when the requested name is one of ours it creates the service itself and the
+ * factory skips the repository.  MLT_CUDA_OVERRIDE=0 turns this off (aliases only).
+ */
+#include "cuda_module.h"
+
+#include <limits.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+static const char *base_name(const char *id)
+{
+    return id && !strncmp(id, "cuda.", 5) ? id + 5 : id;
+}
+
+static void *create_transition(mlt_profile profile, mlt_service_type type, const char *id, const void *arg)
+{
+    const char *n = base_name(id);
+    if (!strcmp(n, "composite"))
+        return cuda_transition_composite_init(profile, type, id, (char *) arg);
+    if (!strcmp(n, "luma"))
+        return cuda_transition_luma_init(profile, type, id, (char *) arg);
+    if (!strcmp(n, "affine"))
+        return cuda_transition_affine_init(profile, type, id, (char *) arg);
+    return NULL;
+}
+
+static void *create_filter(mlt_profile profile, mlt_service_type type, const char *id, const void *arg)
+{
+    if (!strcmp(base_name(id), "imageconvert"))
+        return cuda_filter_imageconvert_init(profile, type, id, (char *) arg);
+    return NULL;
+}
+
+static int override_enabled(void)
+{
+    const char *e = getenv("MLT_CUDA_OVERRIDE");
+    return !(e && (!strcmp(e, "0") || !strcmp(e, "off") || !strcmp(e, "no")));
+}
+
+static void on_transition_request(mlt_properties owner, void *unused, mlt_event_data ev)
+{
+    mlt_factory_event_data *d = mlt_event_data_to_object(ev);
+    if (!d || !d->name || !d->service || *(void **) d->service || !override_enabled())
+        return;
+    if (!strcmp(d->name, "composite") || !strcmp(d->name, "luma") || !strcmp(d->name, "affine"))
+        *(void **) d->service = create_transition(NULL, mlt_service_transition_type, d->name, d->input);
+}
+
+static void on_filter_request(mlt_properties owner, void *unused, mlt_event_data ev)
+{
+    mlt_factory_event_data *d = mlt_event_data_to_object(ev);
+    if (!d || !d->name || !d->service || *(void **) d->service || !override_enabled())
+        return;
+    if (!strcmp(d->name, "imageconvert"))
+        *(void **) d->service = create_filter(NULL, mlt_service_filter_type, d->name, d->input);
+}
+
+static mlt_properties metadata(mlt_service_type type, const char *id, void *data)
+{
+    char file[PATH_MAX];
+    snprintf(file, sizeof(file), "%s/cuda/%s", mlt_environment("MLT_DATA"), (char *) data);
+    return mlt_properties_parse_yaml(file);
+}
+
+MLT_REPOSITORY
+{
+    static const char *transitions[] = {"composite", "luma", "affine"};
+    static char yml[4][64];
+    for (int i = 0; i < 3; i++) {
+        char alias[32];
+        snprintf(alias, sizeof(alias), "cuda.%s", transitions[i]);
+        snprintf(yml[i], sizeof(yml[i]), "transition_%s.yml", transitions[i]);
+        MLT_REGISTER(mlt_service_transition_type, alias, create_transition);
+        MLT_REGISTER_METADATA(mlt_service_transition_type, alias, metadata, yml[i]);
+        if (override_enabled()) {
+            MLT_REGISTER(mlt_service_transition_type, transitions[i], create_transition);
+            MLT_REGISTER_METADATA(mlt_service_transition_type, transitions[i], metadata, yml[i]);
+        }
+    }
+    snprintf(yml[3], sizeof(yml[3]), "filter_imageconvert.yml");
+    MLT_REGISTER(mlt_service_filter_type, "cuda.imageconvert", create_filter);
+    MLT_REGISTER_METADATA(mlt_service_filter_type, "cuda.imageconvert", metadata, yml[3]);
+    if (override_enabled()) {
+        MLT_REGISTER(mlt_service_filter_type, "imageconvert", create_filter);
+        MLT_REGISTER_METADATA(mlt_service_filter_type, "imageconvert", metadata, yml[3]);
+    }
+    mlt_properties events = mlt_factory_event_object();
+    if (events) {
+        mlt_events_listen(events, NULL, "transition-create-request", (mlt_listener) on_transition_request);
+        mlt_events_listen(events, NULL, "filter-create-request", (mlt_listener) on_filter_request);
+    }
+}
