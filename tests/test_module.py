@@ -1,0 +1,188 @@
+"""The MLT module (libmltcuda.so) inside the reference's own melt / libmlt-7 (oracle/_ref).
+
+CPU tier: the module loads through mlt_repository, registers the reference's service names plus the
+cuda.* aliases, serves its metadata, and fails loudly without a GPU.
+GPU tier: whole frames rendered through the public MLT API with the stock services (override off)
+and with the CUDA services (override on) from the same melt command line must agree -- bit-exact
+for composite / luma / imageconvert, +-1 LSB (rgba) for affine.
+"""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import mltenv
+
+pytestmark = pytest.mark.skipif(not (mltenv.have_reference() and mltenv.have_module()),
+                                reason="oracle/_ref or libmltcuda.so not built")
+
+NOISE_B = ["-track", "noise:", "out=249", "-attach", "mirror:flip"]
+A = ["noise:", "out=249"]
+
+
+def melt_query(tmp_path, what):
+    e = mltenv.env(str(tmp_path), cuda=True)
+    return subprocess.run([mltenv.MELT, "-query", what], env=e, capture_output=True, text=True).stdout
+
+
+def test_module_registers_reference_names_and_aliases(tmp_path):
+    out = melt_query(tmp_path, "transitions")
+    for n in ("composite", "luma", "affine", "cuda.composite", "cuda.luma", "cuda.affine"):
+        assert f"- {n}\n" in out
+    out = melt_query(tmp_path, "filters")
+    assert "- imageconvert\n" in out and "- cuda.imageconvert\n" in out
+    # the reference names now resolve to the CUDA metadata
+    assert "(CUDA)" in melt_query(tmp_path, "transition=composite")
+    assert "(CUDA)" in melt_query(tmp_path, "transition=cuda.affine")
+
+
+def test_module_exports_mlt_register():
+    out = subprocess.check_output(["nm", "-D", "--defined-only", mltenv.MODULE]).decode()
+    assert " T mlt_register" in out
+
+
+def dump(tmp_path, tag, cuda, profile, fmt, frames, args, rescale="bilinear", extra=None):
+    prefix = str(tmp_path / tag)
+    ex = {"MLT_DUMP_RESCALE": rescale}
+    ex.update(extra or {})
+    e = mltenv.env(str(tmp_path), cuda=True, override=cuda, extra=ex)
+    r = subprocess.run([mltenv.DUMP, profile, fmt, prefix, ",".join(map(str, frames)), "--"] + args, env=e,
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
+    res = {}
+    for f in frames:
+        img = np.fromfile(f"{prefix}.{f}.img", np.uint8)
+        ap = f"{prefix}.{f}.alpha"
+        res[f] = (img, np.fromfile(ap, np.uint8) if os.path.exists(ap) else None)
+    return res, r.stderr
+
+
+def test_module_fails_loudly_without_gpu(tmp_path):
+    from mlt_b200 import abi
+    if abi.load().mltcuda_device_count() > 0:
+        pytest.skip("a GPU is visible")
+    _, err = dump(tmp_path, "nogpu", True, "atsc_1080p_25", "yuv422", [3],
+                  A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=0/0:100%x100%:50%"])
+    assert "no usable CUDA device" in err and "no CPU fallback" in err
+
+
+# ---- GPU tier -------------------------------------------------------------------------------------
+
+EXACT = [
+    ("cfg1a_blit", "yuv422", [10], A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1"]),
+    ("cfg1b_blend", "yuv422", [10],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=0/0:100%x100%:50%"]),
+    ("cfg1c_subrect", "yuv422", [10],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=25%/25%:50%x50%:50%"]),
+    ("cfg1d_alpha_b", "yuv422", [10],
+     A + ["-track", "colour:0x3060c0a0", "out=249", "-transition", "composite", "a_track=0", "b_track=1",
+          "geometry=10%/10%:50%x50%:70%"]),
+    ("comp_keyframed_odd", "yuv422", [0, 77, 249],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1",
+                    "geometry=0=3/5:641x355:30%; 249=-101/-33:1501x901:90%"]),
+    ("comp_luma_soft", "yuv422", [60],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=0/0:100%x100%:60%",
+                    f"luma={mltenv.LUMA_PGM}", "softness=0.3"]),
+    ("comp_luma_invert", "yuv422", [60],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=10%/10%:80%x80%:40%",
+                    f"luma={mltenv.LUMA_PGM}", "luma_invert=1"]),
+    ("comp_xor_alpha", "yuv422", [10],
+     A + ["-track", "colour:0x3060c0a0", "out=249", "-transition", "composite", "a_track=0", "b_track=1",
+          "geometry=10%/10%:50%x50%:70%", "operator=xor"]),
+    ("comp_halign_distort", "yuv422", [10],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=5%/5%:60%x30%:75%",
+                    "halign=centre", "valign=bottom"]),
+    ("comp_crop", "yuv422", [10],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=10%/10%:50%x50%:100%",
+                    "crop=100/50:50%x50%"]),
+    ("comp_fields", "yuv422", [10],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=0=0/0:50%x50%:50%; 249=50%/50%:50%x50%",
+                    "progressive=0"]),
+    ("cfg2_luma_wipe", "yuv422", [100],
+     A + NOISE_B + ["-transition", f"luma:{mltenv.LUMA_PGM}", "softness=0.2", "in=0", "out=249", "a_track=0", "b_track=1"]),
+    ("luma_wipe_reverse_invert", "yuv422", [40],
+     A + NOISE_B + ["-transition", f"luma:{mltenv.LUMA_PGM}", "softness=0.1", "reverse=1", "invert=1", "in=0", "out=249",
+                    "a_track=0", "b_track=1"]),
+    ("cfg2_dissolve", "yuv422", [100], A + NOISE_B + ["-transition", "luma", "in=0", "out=249", "a_track=0", "b_track=1"]),
+    ("luma_wipe_rgba", "rgba", [100],
+     A + NOISE_B + ["-transition", f"luma:{mltenv.LUMA_PGM}", "softness=0.2", "in=0", "out=249", "a_track=0", "b_track=1"]),
+    ("two_composites", "yuv422", [5],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=5%/5%:40%x40%:80%", "-track",
+                    "noise:", "out=249", "-transition", "composite", "a_track=0", "b_track=2",
+                    "geometry=55%/55%:40%x40%:100%"]),
+    ("imageconvert_rgba_out", "rgba", [10],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=0/0:100%x100%:50%"]),
+    ("imageconvert_rgb_out", "rgb", [10],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=25%/25%:50%x50%:50%"]),
+    ("imageconvert_yuv420p_out", "yuv420p", [10],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=25%/25%:50%x50%:50%"]),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,fmt,frames,args", EXACT, ids=[c[0] for c in EXACT])
+def test_cuda_services_match_stock_services_exactly(tmp_path, name, fmt, frames, args):
+    ref, _ = dump(tmp_path, "ref", False, "atsc_1080p_25", fmt, frames, args)
+    got, err = dump(tmp_path, "cuda", True, "atsc_1080p_25", fmt, frames, args)
+    assert "[cuda]" not in err.replace("[cuda] worker", ""), err[-1500:]
+    for f in frames:
+        assert ref[f][0].shape == got[f][0].shape
+        bad = np.flatnonzero(ref[f][0] != got[f][0])
+        assert bad.size == 0, f"frame {f}: {bad.size} differing bytes, first at {bad[:5]}"
+        assert (ref[f][1] is None) == (got[f][1] is None)
+        if ref[f][1] is not None:
+            assert np.array_equal(ref[f][1], got[f][1])
+
+
+AFFINE_B = ["-track", "noise:", "out=249", "meta.media.width=1920", "meta.media.height=1080", "-attach", "mirror:flip"]
+CLOSE = [
+    ("cfg3_affine_rgba", "rgba", [100], "bilinear",
+     A + AFFINE_B + ["-transition", "affine", "rect=0=10%/10%:50%x50%:100%; 249=30%/30%:70%x70%:60%", "rotate_x=1", "in=0",
+                     "out=249", "a_track=0", "b_track=1"]),
+    ("cfg3_affine_yuv", "yuv422", [100], "bilinear",
+     A + AFFINE_B + ["-transition", "affine", "rect=0=10%/10%:50%x50%:100%; 249=30%/30%:70%x70%:60%", "rotate_x=1", "in=0",
+                     "out=249", "a_track=0", "b_track=1"]),
+    ("affine_nearest_shear", "rgba", [30], "nearest",
+     A + AFFINE_B + ["-transition", "affine", "rect=20%/10%:60%x60%:80%", "fix_shear_x=12", "fix_rotate_x=-20",
+                     "a_track=0", "b_track=1"]),
+    ("affine_bicubic_keyed", "rgba", [30], "bicubic",
+     A + AFFINE_B + ["-transition", "affine", "rect=20%/10%:60%x60%:80%", "keyed=1", "rotate_x=0=0; 249=90", "ox=0=0; 249=300",
+                     "a_track=0", "b_track=1"]),
+    ("affine_colour_b_alpha", "rgba", [30], "bilinear",
+     A + ["-track", "colour:0x3060c0a0", "out=249", "-transition", "affine", "rect=20%/20%:50%x50%:90%", "rotate_x=0.5",
+          "b_alpha=1", "halign=centre", "valign=middle", "a_track=0", "b_track=1"]),
+    ("cfg4_1080p", "yuv422", [0, 37], "bilinear",
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=5%/5%:40%x40%:80%", "-track",
+                    "colour:0x3060c0a0", "out=599", "-transition", "affine", "a_track=0", "b_track=2",
+                    "rect=0=20%/20%:50%x50%:90%; 599=30%/25%:60%x60%:70%", "rotate_x=0.5", "-track", "noise:", "out=599",
+                    "-transition", "composite", "a_track=0", "b_track=3", "geometry=55%/55%:40%x40%:100%"]),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,fmt,frames,rescale,args", CLOSE, ids=[c[0] for c in CLOSE])
+def test_cuda_affine_matches_stock_within_1lsb(tmp_path, name, fmt, frames, rescale, args):
+    ref, _ = dump(tmp_path, "ref", False, "atsc_1080p_25", fmt, frames, args, rescale)
+    got, err = dump(tmp_path, "cuda", True, "atsc_1080p_25", fmt, frames, args, rescale)
+    for f in frames:
+        assert ref[f][0].shape == got[f][0].shape
+        diff = np.abs(ref[f][0].astype(int) - got[f][0].astype(int))
+        # rgba: +-1 LSB on the float-sampled pixels; yuv422: a +-1 rgb step moves Y/U/V by <= 1
+        assert diff.max() <= (1 if fmt == "rgba" else 2), f"frame {f}: max diff {diff.max()}"
+        assert (diff > 0).mean() < 0.02, f"frame {f}: {(diff > 0).mean():.4f} of bytes differ"
+        if ref[f][1] is not None:
+            assert got[f][1] is not None
+            assert np.abs(ref[f][1].astype(int) - got[f][1].astype(int)).max() <= 1
+
+
+@pytest.mark.gpu
+def test_melt_renders_with_worker_threads(tmp_path):
+    """melt ... -consumer null real_time=-4: four worker threads, one CUDA context each."""
+    e = mltenv.env(str(tmp_path), cuda=True)
+    args = A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=25%/25%:50%x50%:50%"]
+    args = [a.replace("out=249", "out=59") for a in args]
+    r = subprocess.run([mltenv.MELT, "-profile", "atsc_1080p_25"] + args + ["-consumer", "null", "real_time=-4", "-silent"],
+                       env=e, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "no usable CUDA device" not in r.stderr and "failed" not in r.stderr
