@@ -174,7 +174,7 @@ int mc_fill_affine_params(AffineParams &p, const mltcuda_affine_desc *d)
 {
     p.m00 = d->matrix[0][0], p.m01 = d->matrix[0][1], p.m02 = d->matrix[0][2];
     p.m10 = d->matrix[1][0], p.m11 = d->matrix[1][1], p.m12 = d->matrix[1][2];
-    p.lower_x = d->lower_x, p.lower_y = d->lower_y, p.dz = d->dz;
+    p.lower_x = d->lower_x, p.lower_y = d->lower_y, p.dz = d->dz, p.rdz = 1.0 / d->dz;
     p.x_offset = d->x_offset, p.y_offset = d->y_offset;
     p.minima = d->minima, p.xmax = d->xmax, p.ymax = d->ymax;
     p.mix = (float) d->mix;

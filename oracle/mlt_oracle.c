@@ -669,6 +669,18 @@ static inline uint32_t orc_f2u(float f, uint32_t mask)
     return (uint32_t) i & mask;
 }
 
+/* Operation order switch.  0 = the C source read literally (strict IEEE, no reassociation).
+ * 1 = the order the reference's Release build actually executes (gcc -O3 -ffast-math on x86-64,
+ * read off the disassembly of oracle/_ref/lib/mlt/libmltplus.so): `a / maxv * o` is evaluated as
+ * a * (o * (1/maxv)), `d / maxv` as d * (1/maxv), `/ j` as * (1/j), and sliced_proc hoists
+ * (m01*y + m02) per row and multiplies by 1/dz.  tests/test_oracle_pinning.py checks mode 1
+ * against the compiled interp*_b32/_b64 with ZERO mismatches for NN and BL. */
+static int g_compiled_order = 0;
+ORC_API void orc_set_compiled_order(int on)
+{
+    g_compiled_order = on;
+}
+
 /* one sample+blend; bits 8 or 16; kind 0 NN (:50-86), 1 BL (:90-194), 2 BC (:198-334) */
 static void orc_interp(int bits, int kind, const void *sv, int w, int h, float x, float y, float o,
                        void *dv, int is_atop)
@@ -688,6 +700,10 @@ static void orc_interp(int bits, int kind, const void *sv, int w, int h, float x
         int p = (int) rintf(x) * 4 + (int) rintf(y) * 4 * w;
         float alpha_s = (float) S(p + 3) / maxv * o;
         float alpha_d = (float) D(3) / maxv;
+        if (g_compiled_order) {
+            alpha_s = (float) S(p + 3) * (o * (1.0f / maxv));
+            alpha_d = (float) D(3) * (1.0f / maxv);
+        }
         float alpha = alpha_s + alpha_d - alpha_s * alpha_d;
         if (is_atop)
             SETD(3, S(p + 3));
@@ -709,10 +725,10 @@ static void orc_interp(int bits, int kind, const void *sv, int w, int h, float x
         float a = S(k + 3) + (S(k1 + 3) - S(k + 3)) * fx;
         float b = S(l + 3) + (S(l1 + 3) - S(l + 3)) * fx;
         float alpha_s = a + (b - a) * fy;
-        float alpha_d = (float) D(3) / maxv;
+        float alpha_d = g_compiled_order ? (float) D(3) * (1.0f / maxv) : (float) D(3) / maxv;
         if (is_atop)
             SETD(3, orc_f2u(alpha_s, mask));
-        alpha_s = alpha_s / maxv * o;
+        alpha_s = g_compiled_order ? alpha_s * (o * (1.0f / maxv)) : alpha_s / maxv * o;
         float alpha = alpha_s + alpha_d - alpha_s * alpha_d;
         if (!is_atop)
             SETD(3, orc_f2u(maxv * alpha, mask));
@@ -743,7 +759,7 @@ static void orc_interp(int bits, int kind, const void *sv, int w, int h, float x
             }
             for (int j = 1; j < 4; j++)
                 for (int i = 3; i >= j; i--) {
-                    float kk = (y - i - n) / j;
+                    float kk = g_compiled_order ? (y - i - n) * (1.0f / j) : (y - i - n) / j;
                     for (int c = 0; c < 4; c++)
                         pc[c][i] = pc[c][i] + kk * (pc[c][i] - pc[c][i - 1]);
                 }
@@ -751,14 +767,14 @@ static void orc_interp(int bits, int kind, const void *sv, int w, int h, float x
                 p[c] = pc[c][3];
             for (int j = 1; j < 4; j++)
                 for (int i = 3; i >= j; i--)
-                    p[i] = p[i] + (x - i - m) / j * (p[i] - p[i - 1]);
+                    p[i] = p[i] + (g_compiled_order ? (x - i - m) * (1.0f / j) : (x - i - m) / j) * (p[i] - p[i - 1]);
             if (p[3] < 0.0f)
                 p[3] = 0.0f;
             if (p[3] > maxv)
                 p[3] = maxv;
             if (b == 3) {
-                float alpha_s = p[3] / maxv * o;
-                float alpha_d = (float) D(3) / maxv;
+                float alpha_s = g_compiled_order ? p[3] * (o * (1.0f / maxv)) : p[3] / maxv * o;
+                float alpha_d = g_compiled_order ? (float) D(3) * (1.0f / maxv) : (float) D(3) / maxv;
                 alpha = alpha_s + alpha_d - alpha_s * alpha_d;
                 SETD(3, is_atop ? orc_f2u(p[3], mask) : orc_f2u(maxv * alpha, mask));
                 alpha = alpha_s / alpha;
@@ -787,11 +803,17 @@ ORC_API long orc_affine(int bits, void *a_image, const void *b_image, int a_widt
     long covered = 0;
     size_t px = bits == 8 ? 4 : 8;
     double y = lower_y;
+    const double rdz = 1.0 / dz;
     for (int i = 0; i < a_height; i++, y++) {
         double x = lower_x;
+        const double rowx = m[1] * y + m[2], rowy = m[4] * y + m[5];
         for (int j = 0; j < a_width; j++, x++) {
             double dx = (m[0] * x + m[1] * y + m[2]) / dz + x_offset;
             double dy = (m[3] * x + m[4] * y + m[5]) / dz + y_offset;
+            if (g_compiled_order) {
+                dx = (m[0] * x + rowx) * rdz + x_offset;
+                dy = (m[3] * x + rowy) * rdz + y_offset;
+            }
             if (dx >= minima && dx <= xmax && dy >= minima && dy <= ymax) {
                 orc_interp(bits, interp, b_image, b_width, b_height, (float) dx, (float) dy,
                            (float) mix, (uint8_t *) a_image + ((size_t) i * a_width + j) * px,

@@ -25,6 +25,9 @@ def lib():
             subprocess.check_call(["make", "-C", ORACLE_DIR, "liboracle.so"], stdout=subprocess.DEVNULL)
         _lib = C.CDLL(LIB)
         _lib.orc_affine.restype = C.c_long
+        # oracle of record = the Release x86-64 build: float paths in the operation order
+        # that build executes; test_oracle_pinning.py checks both orders against the compiled .so
+        _lib.orc_set_compiled_order(C.c_int(1))
     return _lib
 
 
@@ -115,6 +118,11 @@ def dissolve_rgba(bits, dest, src, w, h, weight):
     d = dest.copy()
     lib().orc_dissolve_rgba(bits, _p(d), _p(src), w, h, C.c_float(weight))
     return d
+
+
+def set_compiled_order(on):
+    """1 = operation order of the reference's -ffast-math Release build (see mlt_oracle.c)."""
+    lib().orc_set_compiled_order(C.c_int(1 if on else 0))
 
 
 def interp_px(bits, kind, s, w, h, x, y, o, d, is_atop):

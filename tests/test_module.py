@@ -95,7 +95,7 @@ EXACT = [
                     "halign=centre", "valign=bottom"]),
     ("comp_crop", "yuv422", [10],
      A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=10%/10%:50%x50%:100%",
-                    "crop=100/50:50%x50%"]),
+                    "crop=-100/-50:960x540"]),
     ("comp_fields", "yuv422", [10],
      A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=0=0/0:50%x50%:50%; 249=50%/50%:50%x50%",
                     "progressive=0"]),
