@@ -168,9 +168,12 @@ def test_cuda_affine_matches_stock_within_1lsb(tmp_path, name, fmt, frames, resc
     for f in frames:
         assert ref[f][0].shape == got[f][0].shape
         diff = np.abs(ref[f][0].astype(int) - got[f][0].astype(int))
-        # rgba: +-1 LSB on the float-sampled pixels; yuv422: a +-1 rgb step moves Y/U/V by <= 1
+        print(f"{name} frame {f}: {int((diff > 0).sum())} of {diff.size} bytes differ, max {int(diff.max())}")
+        # spec: +-1 LSB (rgba).  The kernels follow the Release build's operation order, so in
+        # practice frames are identical except where the double-precision x++ stepping of the
+        # reference rounds differently from lower_x + j (a handful of pixels at most).
         assert diff.max() <= (1 if fmt == "rgba" else 2), f"frame {f}: max diff {diff.max()}"
-        assert (diff > 0).mean() < 0.02, f"frame {f}: {(diff > 0).mean():.4f} of bytes differ"
+        assert (diff > 0).mean() < 1e-4, f"frame {f}: {(diff > 0).mean():.6f} of bytes differ"
         if ref[f][1] is not None:
             assert got[f][1] is not None
             assert np.abs(ref[f][1].astype(int) - got[f][1].astype(int)).max() <= 1
