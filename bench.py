@@ -201,7 +201,7 @@ def run_ours(args, dist):
     ctx = Context(dev)
     ctx2 = Context(dev)  # second stream for the double-buffered end-to-end leg
     F = FRAMES_PER_STEP
-    first = dist.rank * F  # each rank renders its own slice of the timeline
+    first = workloads.shard_frames(dist.rank, dist.world, F)[0]  # each rank renders its own slice of the timeline
     frames = [workloads.cfg4_frame(first + i, W, H) for i in range(F)]
     (g1, b1w, b1h), (g2, b2w, b2h) = frames[0]["comp1"], frames[0]["comp2"]
     fb, b1b, b3b = W * H * 2, b1w * b1h * 2, b2w * b2h * 2

@@ -112,3 +112,11 @@ def cfg4_frame(position, W=W_UHD, H=H_UHD, cfg=CFG4):
     rect_px = [r[0] * W, r[1] * H, r[2] * W, r[3] * H, r[4]]
     aff = affine_params(W, H, rect_px, position, cfg["rotate_x"], W, H, "bilinear")
     return dict(W=W, H=H, comp1=(g1, b1w, b1h), comp2=(g2, b2w, b2h), affine=aff)
+
+
+def shard_frames(rank, world, frames_per_rank, step=0):
+    """Frame-parallel sharding of a timeline over `world` GPUs: frames are independent,
+    so rank r renders the contiguous block [r*F, (r+1)*F) of every step's world*F frames.  No data
+    exchange is needed; order is restored by frame index."""
+    base = step * world * frames_per_rank + rank * frames_per_rank
+    return list(range(base, base + frames_per_rank))

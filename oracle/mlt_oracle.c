@@ -905,3 +905,14 @@ ORC_API void orc_colour(void *dst, uint8_t *dst_alpha, int format, int width, in
             *p++ = r, *p++ = g, *p++ = b;
     }
 }
+
+/* FNV-1a 64 over a buffer, as oracle/mlt_dump.c hashes the reference's frames */
+ORC_API uint64_t orc_fnv1a64(const uint8_t *p, size_t n)
+{
+    uint64_t h = 1469598103934665603ULL;
+    for (size_t i = 0; i < n; i++) {
+        h ^= p[i];
+        h *= 1099511628211ULL;
+    }
+    return h;
+}
