@@ -31,14 +31,11 @@ struct CompK
 
 __global__ void __launch_bounds__(256) k_composite_rows(CompK K)
 {
-    long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
-    long long total = (long long) K.cpr * K.rows * K.batch;
-    if (gid >= total)
+    // grid = (chunks of a row, row, frame): no div/mod in the index math
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= K.cpr)
         return;
-    int c = (int) (gid % K.cpr);
-    long long t = gid / K.cpr;
-    int r = (int) (t % K.rows);
-    int b = (int) (t / K.rows);
+    const int r = blockIdx.y, b = blockIdx.z;
     const CompositeParams &P = K.p;
 
     uintptr_t drow = (uintptr_t) (K.dest + b * K.dest_bs + r * K.stride_dest);
@@ -112,6 +109,7 @@ void mc_fill_composite_params(CompositeParams &p, const mltcuda_composite_desc *
     p.weight = d->weight, p.softness = d->softness, p.step = d->step, p.op = d->op;
     p.has_ab = d->alpha_b != nullptr, p.has_aa = d->alpha_a != nullptr, p.has_luma = d->luma != nullptr;
     p.w8 = d->weight >> 8;
+    p.soft_magic = mc_div_magic((uint32_t) d->softness);
     p.n8 = 0, p.blit = 0, p.premul = 0;
     // transition_composite.c:156-167: SSE2 routine only for composite_line_yuv itself (op over)
     if (d->op == MLTCUDA_OP_OVER && !d->scalar_only && !d->luma && d->width > 7) {
@@ -144,8 +142,9 @@ extern "C" int mltcuda_composite(mltcuda_ctx *ctx, const mltcuda_composite_desc 
     if (K.batch > 1)
         MC_BADARG(!K.dest_bs, "batch > 1 needs dest_bstride");
     K.cpr = (d->width + 7 + 7) / 8; // up to 7 head pixels before the first composited pixel
-    long long total = (long long) K.cpr * K.rows * K.batch;
-    k_composite_rows<<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);
+    MC_BADARG(K.rows > 65535 || K.batch > 65535, "more than 65535 rows / frames in one launch");
+    dim3 grd((K.cpr + 127) / 128, K.rows, K.batch);
+    k_composite_rows<<<grd, 128, 0, ctx->stream>>>(K);
     return mc_after_launch(ctx, "k_composite_rows");
 }
 

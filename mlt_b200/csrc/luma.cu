@@ -48,6 +48,7 @@ struct LumaK
     int width_src, height_src, width_dest; // after the min() of :376-377
     int x_diff, y_diff;
     uint32_t i_softness;
+    uint64_t soft_magic; // mc_div_magic(i_softness)
     float softness, field_pos0, field_pos1;
     int field_count, invert, alpha_over;
     const int *flag; // translucent flag on device (may be NULL => forced value)
@@ -76,14 +77,10 @@ __device__ __forceinline__ void luma_row_info(const LumaK &K, int i, int &field,
 // luma_composite_yuv422 (:327-473) and, with map == NULL, dissolve_yuv422 (:131-190)
 template <bool DISSOLVE> __global__ void __launch_bounds__(256) k_luma_yuv422(LumaK K)
 {
-    long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
-    long long total = (long long) K.cpr * K.height_src * K.batch;
-    if (gid >= total)
+    const int c = blockIdx.x * blockDim.x + threadIdx.x; // grid = (chunks of a row, row, frame)
+    if (c >= K.cpr)
         return;
-    int c = (int) (gid % K.cpr);
-    long long t = gid / K.cpr;
-    int i = (int) (t % K.height_src);
-    int b = (int) (t / K.height_src);
+    const int i = blockIdx.y, b = blockIdx.z;
     const int translucent = K.flag ? *K.flag : K.forced;
 
     uintptr_t drow = (uintptr_t) (K.dest + b * K.dest_bs + (size_t) i * K.width_dest * 2);
@@ -162,7 +159,7 @@ template <bool DISSOLVE> __global__ void __launch_bounds__(256) k_luma_yuv422(Lu
             } else { // :452-463
                 uint32_t weight = __ldg(l + ((j * K.x_diff) >> 16));
                 uint32_t value = (uint32_t) mc_smoothstep((int32_t) weight, (int32_t) (K.i_softness + weight),
-                                                          (uint32_t) ((1 << 16) * fpos));
+                                                          (uint32_t) ((1 << 16) * fpos), K.soft_magic);
                 qy = (py * value + qy * ((1u << 16) - value)) >> 16;
                 qc = (pc * value + qc * ((1u << 16) - value)) >> 16;
                 res = (qy & 0xff) | ((qc & 0xff) << 8);
@@ -194,14 +191,15 @@ template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256) k_lu
     const int w = K.width_src, h = K.height_src;
     const long long npx = (long long) w * h;
     const long long cpf = (npx + PPT - 1) / PPT;
-    long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
-    if (gid >= cpf * K.batch)
+    // grid = (groups of a frame, 1, frame); a frame has < 2^31 pixels, so 32-bit index math
+    const unsigned gid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (unsigned) cpf)
         return;
-    int b = (int) (gid / cpf);
-    long long p0 = (gid % cpf) * PPT;
+    const int b = blockIdx.z;
+    const unsigned p0 = gid * PPT;
     const int translucent = K.flag ? *K.flag : K.forced;
-    T *q = reinterpret_cast<T *>(K.dest + b * K.dest_bs) + p0 * 4;
-    const T *p = reinterpret_cast<const T *>(K.src + b * K.src_bs) + p0 * 4;
+    T *q = reinterpret_cast<T *>(K.dest + b * K.dest_bs) + (size_t) p0 * 4;
+    const T *p = reinterpret_cast<const T *>(K.src + b * K.src_bs) + (size_t) p0 * 4;
     uint32_t qv[PPT][4], pv[PPT][4];
     const bool full = p0 + PPT <= npx;
     if (full) {
@@ -226,7 +224,10 @@ template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256) k_lu
                 qv[k][c] = ok ? q[4 * k + c] : 0, pv[k][c] = ok ? p[4 * k + c] : 0;
             }
     }
-    int i = (int) (p0 / w), j = (int) (p0 % w);
+    int i = (int) (p0 / (unsigned) w), j = (int) (p0 - (unsigned) i * (unsigned) w);
+    int field = 0, y_off = 0, ordinal = 0;
+    const uint16_t *lrow = nullptr;
+    float fpos = 0.f;
 #pragma unroll
     for (int k = 0; k < PPT; k++) {
         if (p0 + k < npx) {
@@ -241,10 +242,12 @@ template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256) k_lu
                     qv[k][c] = mc_f2u(pv[k][c] * mix_b + qv[k][c] * (1.f - mix_b), mask);
                 qv[k][3] = mc_f2u(maxv * mix2, mask);
             } else {
-                int field, y_off, ordinal;
-                luma_row_info(K, i, field, y_off, ordinal);
-                const float fpos = field ? K.field_pos1 : K.field_pos0;
-                uint32_t lw = __ldg(K.map + (long) (y_off >> 16) * (K.luma_width * K.field_count) + ((j * K.x_diff) >> 16));
+                if (k == 0 || j == 0) { // row-dependent terms: once per thread unless the group wraps
+                    luma_row_info(K, i, field, y_off, ordinal);
+                    fpos = field ? K.field_pos1 : K.field_pos0;
+                    lrow = K.map + (long) (y_off >> 16) * (K.luma_width * K.field_count);
+                }
+                uint32_t lw = __ldg(lrow + ((j * K.x_diff) >> 16));
                 if (translucent) {
                     float weight = (float) lw / 65535.f;
                     float value = mc_smoothstep_f(weight, K.softness + weight, fpos);
@@ -265,7 +268,7 @@ template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256) k_lu
                         qv[k][c] = mc_f2u(pv[k][c] * mix_b + qv[k][c] * (1.f - mix_b), mask);
                 } else {
                     uint32_t value = (uint32_t) mc_smoothstep((int32_t) lw, (int32_t) (K.i_softness + lw),
-                                                              (uint32_t) ((1 << 16) * fpos));
+                                                              (uint32_t) ((1 << 16) * fpos), K.soft_magic);
 #pragma unroll
                     for (int c = 0; c < 3; c++)
                         qv[k][c] = ((pv[k][c] * value + qv[k][c] * ((1u << 16) - value)) >> 16) & mask;
@@ -338,6 +341,7 @@ extern "C" int mltcuda_luma(mltcuda_ctx *ctx, const mltcuda_luma_desc *d)
     K.invert = d->invert, K.alpha_over = d->alpha_over;
     K.softness = d->softness;
     K.i_softness = (uint32_t) (d->softness * (1 << 16));
+    K.soft_magic = mc_div_magic(K.i_softness);
     K.field_count = d->field_order < 0 ? 1 : 2;
     K.field_pos0 = (d->pos + ((d->field_order == 0 ? 1 : 0) * d->frame_delta * 0.5f)) * (1.f + d->softness);
     K.field_pos1 = (d->pos + ((d->field_order == 0 ? 0 : 1) * d->frame_delta * 0.5f)) * (1.f + d->softness);
@@ -397,10 +401,12 @@ extern "C" int mltcuda_luma(mltcuda_ctx *ctx, const mltcuda_luma_desc *d)
         K.cpr = (K.width_src + 14) / 8;
         long long total = (long long) K.cpr * K.height_src * K.batch;
         if (total > 0) {
+            MC_BADARG(K.height_src > 65535 || K.batch > 65535, "more than 65535 rows / frames in one launch");
+            dim3 grd((K.cpr + 127) / 128, K.height_src, K.batch);
             if (dissolve)
-                k_luma_yuv422<true><<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);
+                k_luma_yuv422<true><<<grd, 128, 0, ctx->stream>>>(K);
             else
-                k_luma_yuv422<false><<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(K);
+                k_luma_yuv422<false><<<grd, 128, 0, ctx->stream>>>(K);
             rc = mc_after_launch(ctx, "k_luma_yuv422");
         }
     } else {
@@ -419,8 +425,9 @@ extern "C" int mltcuda_luma(mltcuda_ctx *ctx, const mltcuda_luma_desc *d)
         }
         K.rows0 = (K.height_src + 1) / 2;
         const int ppt = fmt == MLTCUDA_FMT_RGBA ? 4 : 2;
-        long long total = (((long long) K.width_src * K.height_src + ppt - 1) / ppt) * K.batch;
-        unsigned blocks = mc_blocks(total, 256);
+        long long per_frame = ((long long) K.width_src * K.height_src + ppt - 1) / ppt;
+        MC_BADARG(per_frame * ppt >= (1ll << 31) || K.batch > 65535, "frame too large / too many frames for one launch");
+        dim3 blocks(mc_blocks(per_frame, 256), 1, K.batch);
         if (fmt == MLTCUDA_FMT_RGBA) {
             if (dissolve)
                 k_luma_rgba<uint8_t, true><<<blocks, 256, 0, ctx->stream>>>(K);

@@ -20,59 +20,71 @@ constexpr uint64_t MOD_A = (uint64_t) MWC_A * 65536u - 1, MOD_B = (uint64_t) MWC
 // table layout (uint32): [gen][level0: 4096][level1: 4096][level2: 256]
 constexpr int TAB_PER_GEN = 4096 + 4096 + 256;
 
-__device__ __forceinline__ uint32_t mwc_pow(const uint32_t *tab, uint64_t mod, uint64_t n)
+// r mod m for r < 2^63, m < 2^32, with M = floor(2^64 / m): Barrett, quotient off by at most 2
+__device__ __forceinline__ uint32_t barrett(uint64_t r, uint64_t m, uint64_t M)
+{
+    uint64_t t = r - __umul64hi(r, M) * m;
+    t = t >= m ? t - m : t;
+    t = t >= m ? t - m : t;
+    return (uint32_t) t;
+}
+
+__device__ __forceinline__ uint32_t mwc_pow(const uint32_t *tab, uint64_t mod, uint64_t M, uint32_t n)
 {
     uint64_t r = __ldg(tab + (n & 4095));
-    r = r * __ldg(tab + 4096 + ((n >> 12) & 4095)) % mod;
-    r = r * __ldg(tab + 8192 + ((n >> 24) & 255)) % mod;
+    r = barrett(r * __ldg(tab + 4096 + ((n >> 12) & 4095)), mod, M);
+    r = barrett(r * __ldg(tab + 8192 + ((n >> 24) & 255)), mod, M);
     return (uint32_t) r;
 }
 
-__global__ void __launch_bounds__(256) k_noise(uint8_t *dst, long long npx, uint32_t x2, uint32_t y2, uint32_t x0,
-                                               uint32_t y0, const uint32_t *tab, int batch, size_t bs,
-                                               int position)
+// The pixel byte is ((x << 16) + (y & 65535)) & 0xff == y & 0xff (producer_noise.c:118): the x
+// generator never reaches the image, so only the y generator (multiplier 30903) is evaluated.
+// One thread = 16 pixels (two 16-byte stores); grid = (groups of a frame, 1, frame).
+constexpr int NOISE_PPT = 16;
+__global__ void __launch_bounds__(256) k_noise(uint8_t *dst, unsigned npx, uint32_t y2, uint32_t y0,
+                                               const uint32_t *tab, size_t bs, int position, uint64_t M)
 {
-    const long long cpf = (npx + 7) / 8;
-    long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
-    if (gid >= cpf * batch)
+    const unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
+    if ((unsigned long long) c * NOISE_PPT >= npx)
         return;
-    int b = (int) (gid / cpf);
-    long long c = gid % cpf;
-    // batch frame b is timeline position `position + b`: re-seed (init_seed :37-43)
-    if (b) {
+    const int b = blockIdx.z;
+    if (b) { // batch frame b is timeline position `position + b`: re-seed (init_seed :37-43)
         uint32_t p = (uint32_t) (position + b);
-        x0 = 521288629u + p - (p << 16), y0 = 362436069u - p + (p << 16);
-        uint32_t x = x0, y = y0;
+        y0 = 362436069u - p + (p << 16);
+        uint32_t y = y0;
         for (int k = 0; k < 2; k++)
-            x = MWC_A * (x & 65535) + (x >> 16), y = MWC_B * (y & 65535) + (y >> 16);
-        x2 = x, y2 = y;
+            y = MWC_B * (y & 65535) + (y >> 16);
+        y2 = y;
     }
-    long long hi = c * 8 + 7 < npx ? c * 8 + 7 : npx - 1; // last pixel of the group
-    long long n = npx - hi;                               // its generation step (1-based)
-    uint32_t x, y;
-    if (n >= 2) {
-        x = (uint32_t) ((uint64_t) mwc_pow(tab, MOD_A, (uint64_t) n - 2) * x2 % MOD_A);
-        y = (uint32_t) ((uint64_t) mwc_pow(tab + TAB_PER_GEN, MOD_B, (uint64_t) n - 2) * y2 % MOD_B);
-    } else { // n == 1
-        x = MWC_A * (x0 & 65535) + (x0 >> 16), y = MWC_B * (y0 & 65535) + (y0 >> 16);
-    }
-    uint32_t w[4] = {0, 0, 0, 0};
-    int cnt = (int) (hi - c * 8) + 1;
+    const unsigned lo = c * NOISE_PPT;
+    const unsigned hi = lo + NOISE_PPT - 1 < npx ? lo + NOISE_PPT - 1 : npx - 1; // last pixel of the group
+    const unsigned n = npx - hi; // its generation step (1-based; the buffer is filled from the end)
+    uint32_t y;
+    if (n >= 2)
+        y = barrett((uint64_t) mwc_pow(tab + TAB_PER_GEN, MOD_B, M, n - 2) * y2, MOD_B, M);
+    else
+        y = MWC_B * (y0 & 65535) + (y0 >> 16);
+    uint32_t w[NOISE_PPT / 2];
 #pragma unroll
-    for (int k = 7; k >= 0; k--) {
+    for (int k = 0; k < NOISE_PPT / 2; k++)
+        w[k] = 0;
+    const int cnt = (int) (hi - lo) + 1;
+#pragma unroll
+    for (int k = NOISE_PPT - 1; k >= 0; k--) {
         if (k < cnt) {
-            uint32_t value = ((x << 16) + (y & 65535)) & 0xff;
+            uint32_t value = y & 0xff;
             value = value < 16 ? 16 : value > 240 ? 240 : value;
             w[k >> 1] |= (value | (128u << 8)) << ((k & 1) * 16);
-            x = MWC_A * (x & 65535) + (x >> 16), y = MWC_B * (y & 65535) + (y >> 16);
+            y = MWC_B * (y & 65535) + (y >> 16);
         }
     }
-    uint8_t *d = dst + b * bs + c * 16;
-    if (cnt == 8) {
-        *reinterpret_cast<uint4 *>(d) = make_uint4(w[0], w[1], w[2], w[3]);
+    uint8_t *d = dst + b * bs + (size_t) lo * 2;
+    if (cnt == NOISE_PPT) {
+        reinterpret_cast<uint4 *>(d)[0] = make_uint4(w[0], w[1], w[2], w[3]);
+        reinterpret_cast<uint4 *>(d)[1] = make_uint4(w[4], w[5], w[6], w[7]);
     } else {
 #pragma unroll
-        for (int k = 0; k < 8; k++)
+        for (int k = 0; k < NOISE_PPT; k++)
             if (k < cnt)
                 reinterpret_cast<uint16_t *>(d)[k] = (uint16_t) (w[k >> 1] >> ((k & 1) * 16));
     }
@@ -172,8 +184,10 @@ extern "C" int mltcuda_noise(mltcuda_ctx *ctx, uint8_t *dst, int width, int heig
     uint32_t x = x0, y = y0;
     for (int k = 0; k < 2; k++)
         x = MWC_A * (x & 65535) + (x >> 16), y = MWC_B * (y & 65535) + (y >> 16);
-    long long total = ((npx + 7) / 8) * batch;
-    k_noise<<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(dst, npx, x, y, x0, y0, ctx->noise_tab, batch, dst_bstride, position);
+    MC_BADARG(npx >= (1ll << 31) || batch > 65535, "frame too large / too many frames for one launch");
+    (void) x, (void) x0;
+    dim3 grd(mc_blocks((npx + NOISE_PPT - 1) / NOISE_PPT, 256), 1, batch);
+    k_noise<<<grd, 256, 0, ctx->stream>>>(dst, (unsigned) npx, y, y0, ctx->noise_tab, dst_bstride, position, ~0ull / MOD_B);
     return mc_after_launch(ctx, "k_noise");
 }
 

@@ -37,6 +37,7 @@ struct TLumaOp
     const uint16_t *map;
     int luma_width, width_src, height_src, x_diff, y_diff;
     uint32_t i_softness, step;
+    uint64_t soft_magic;
     size_t src_bs;
 };
 struct TOp
@@ -164,7 +165,7 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
                     uint32_t dp = (yuv[k >> 1] >> ((k & 1) * 16)) & 0xffff;
                     uint32_t sp = (s[k >> 1] >> ((k & 1) * 16)) & 0xffff;
                     uint32_t w = __ldg(l + ((j * L.x_diff) >> 16));
-                    uint32_t value = (uint32_t) mc_smoothstep((int32_t) w, (int32_t) (L.i_softness + w), L.step);
+                    uint32_t value = (uint32_t) mc_smoothstep((int32_t) w, (int32_t) (L.i_softness + w), L.step, L.soft_magic);
                     uint32_t qy = ((sp & 0xff) * value + (dp & 0xff) * ((1u << 16) - value)) >> 16;
                     uint32_t qc = ((sp >> 8) * value + (dp >> 8) * ((1u << 16) - value)) >> 16;
                     uint32_t res = (qy & 0xff) | ((qc & 0xff) << 8);
@@ -256,6 +257,7 @@ extern "C" int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d)
             t.l.height_src = l.height_src > d->height ? d->height : l.height_src;
             t.l.x_diff = (l.luma_width << 16) / l.width, t.l.y_diff = (l.luma_height << 16) / l.height;
             t.l.i_softness = (uint32_t) (l.softness * (1 << 16));
+            t.l.soft_magic = mc_div_magic(t.l.i_softness);
             float fpos = (l.pos + 0 * l.frame_delta * 0.5f) * (1.f + l.softness);
             t.l.step = (uint32_t) ((1 << 16) * fpos);
             t.l.src_bs = l.src_bstride;
