@@ -265,7 +265,11 @@ int cuda_convert_image(mlt_frame frame, uint8_t **image, mlt_image_format *forma
     if (*format == output && *format != mlt_image_private)
         return 0;
     mlt_properties p = MLT_FRAME_PROPERTIES(frame);
-    const int resident = mlt_properties_get_int(p, CUDA_REQUESTED) > 0; /* a CUDA service is asking */
+    /* Only an explicit request for mlt_image_private made by one of our services keeps pixels in
+     * HBM.  Anything else -- in particular a CPU filter sitting between two CUDA services, which
+     * asks for a host format while an outer CUDA request is still pending on the same frame --
+     * gets an ordinary host image. */
+    const int resident = output == mlt_image_private && mlt_properties_get_int(p, CUDA_REQUESTED) > 0;
     cuda_image ci = cuda_frame_peek(frame, *image, *format);
     if (*format == mlt_image_private && !ci)
         return 1; /* another module's private image */
@@ -332,7 +336,7 @@ cuda_image cuda_frame_get_image(mlt_frame frame, mlt_image_format format, int *w
 {
     mlt_properties p = MLT_FRAME_PROPERTIES(frame);
     uint8_t *img = NULL;
-    mlt_image_format got = format;
+    mlt_image_format got = mlt_image_private; /* ask for residency explicitly (see cuda_convert_image) */
     mlt_frame_prepend_convert_image(frame, cuda_convert_image);
     mlt_properties_set_int(p, CUDA_REQUESTED, mlt_properties_get_int(p, CUDA_REQUESTED) + 1);
     int err = mlt_frame_get_image(frame, &img, &got, width, height, writable);
