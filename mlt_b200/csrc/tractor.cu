@@ -60,7 +60,23 @@ struct TractorK
 
 // ONLY_BL: every affine op of the list samples bilinearly (the default "consumer.rescale"), so the
 // nearest / bicubic samplers are compiled out -- they would otherwise set the register budget.
-template <bool ONLY_BL>
+//
+// SIG: 0 = interpret the op list at run time.  Otherwise the op list itself, 4 bits per slot
+// (1 composite, 2 affine, 3 luma, 4 convert->rgba, 5 convert->yuv422): the loop is fully unrolled,
+// every branch on the op kind folds away and every op parameter becomes an immediate constant-bank
+// operand instead of an indexed LDC.  The host instantiates the common graph shapes (SIGS below)
+// and falls back to SIG 0 for anything else; both run the same code, so results are identical.
+__host__ __device__ constexpr int sig_len(uint32_t sig)
+{
+    int n = 0;
+    while (sig) {
+        n++;
+        sig >>= 4;
+    }
+    return n;
+}
+
+template <bool ONLY_BL, uint32_t SIG>
 __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_constant__ TractorK K)
 {
     // 2-D CTA: 32 groups (256 px) x 8 rows -- no div/mod, and the B taps of neighbouring rows share L1
@@ -89,9 +105,13 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
         rgba[4] = v1.x, rgba[5] = v1.y, rgba[6] = v1.z, rgba[7] = v1.w;
     }
 
-    for (int oi = 0; oi < K.n_ops; oi++) {
+    const int n_ops = SIG ? sig_len(SIG) : K.n_ops;
+#pragma unroll
+    for (int oi = 0; oi < n_ops; oi++) {
         const TOp &op = K.ops[oi];
-        if (op.kind == MLTCUDA_TOP_COMPOSITE) {
+        const int code = SIG ? (int) ((SIG >> (4 * oi)) & 15)
+                             : (op.kind == MLTCUDA_TOP_CONVERT ? (op.to_format == MLTCUDA_FMT_RGBA ? 4 : 5) : op.kind);
+        if (code == 1) {
             const TCompOp &C = op.c;
             int rrel = r - C.y;
             if (rrel < 0 || (C.row_step == 2 && (rrel & 1)))
@@ -116,8 +136,8 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
             mc_composite_group8(C.cp, j0, jlo, jhi, yuv, s, ab, na, lum);
             if (has_alpha)
                 al[0] = na[0], al[1] = na[1];
-        } else if (op.kind == MLTCUDA_TOP_CONVERT) {
-            if (op.to_format == MLTCUDA_FMT_RGBA) { // filter_imageconvert.c:58-111
+        } else if (code == 4 || code == 5) {
+            if (code == 4) { // filter_imageconvert.c:58-111
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
                     uint32_t a0 = has_alpha ? (al[k >> 1] >> ((k & 1) * 16)) & 0xff : 0xff;
@@ -133,7 +153,7 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
                 al[1] = __byte_perm(__byte_perm(rgba[4], rgba[5], 0x0073), __byte_perm(rgba[6], rgba[7], 0x0073), 0x5410);
                 fmt = MLTCUDA_FMT_YUV422, has_alpha = 1;
             }
-        } else if (op.kind == MLTCUDA_TOP_AFFINE) {
+        } else if (code == 2) {
             const AffineParams &P = op.a.ap;
             const AffineRow R = mc_affine_row(P, r);
             if (mc_affine_reject(P, R, col0, 8))
@@ -149,7 +169,7 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
                     rgba[k] = d[0] | (d[1] << 8) | (d[2] << 16) | (d[3] << 24);
                 }
             }
-        } else if (op.kind == MLTCUDA_TOP_LUMA) { // transition_luma.c:452-463, progressive
+        } else if (code == 3) { // transition_luma.c:452-463, progressive
             const TLumaOp &L = op.l;
             if (r >= L.height_src || col0 >= L.width_src)
                 continue;
@@ -269,9 +289,32 @@ extern "C" int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d)
     MC_BADARG(fmt != d->out_format, "out_format does not match the format the op list ends in");
     MC_BADARG((d->height + 7) / 8 > 65535 || K.batch > 65535, "frame too tall / batch too large for one launch");
     dim3 blk(32, 8, 1), grd((d->width / 8 + 31) / 32, (d->height + 7) / 8, K.batch);
-    if (only_bl)
-        k_tractor<true><<<grd, blk, 0, ctx->stream>>>(K);
-    else
-        k_tractor<false><<<grd, blk, 0, ctx->stream>>>(K);
+    // op-list signature (see k_tractor): specialised instantiations for the common graph shapes
+    uint32_t sig = 0;
+    if (only_bl && d->n_ops > 0) {
+        for (int i = d->n_ops - 1; i >= 0; i--) {
+            const mltcuda_tractor_op &o = d->ops[i];
+            uint32_t code = o.kind == MLTCUDA_TOP_CONVERT ? (o.to_format == MLTCUDA_FMT_RGBA ? 4u : 5u) : (uint32_t) o.kind;
+            sig = (sig << 4) | code;
+        }
+    }
+#define MC_TRACTOR_SIG(S) \
+    case S: \
+        k_tractor<true, S><<<grd, blk, 0, ctx->stream>>>(K); \
+        break;
+    switch (only_bl ? sig : 0xffffffffu) {
+        MC_TRACTOR_SIG(0x1)     // composite
+        MC_TRACTOR_SIG(0x11)    // composite x2
+        MC_TRACTOR_SIG(0x111)   // composite x3
+        MC_TRACTOR_SIG(0x3)     // luma wipe
+        MC_TRACTOR_SIG(0x524)   // ->rgba, affine, ->yuv422
+        MC_TRACTOR_SIG(0x15241) // cfg4: composite, ->rgba, affine, ->yuv422, composite
+    default:
+        if (only_bl)
+            k_tractor<true, 0><<<grd, blk, 0, ctx->stream>>>(K);
+        else
+            k_tractor<false, 0><<<grd, blk, 0, ctx->stream>>>(K);
+    }
+#undef MC_TRACTOR_SIG
     return mc_after_launch(ctx, "k_tractor");
 }
