@@ -135,11 +135,22 @@ template <typename T, int INTERP> __global__ void __launch_bounds__(256) k_affin
         return;
     T *q = reinterpret_cast<T *>(K.a_image + b * K.a_bs) + ((size_t) i * K.a_width + j) * 4;
     const T *bimg = reinterpret_cast<const T *>(K.b_image + b * K.b_bs);
+    asm volatile("" : "+l"(bimg)); // keep the batch base in registers: do not re-derive it per pixel
     uint4 a = ld16(q);
     uint32_t aw[4] = {a.x, a.y, a.z, a.w};
 #pragma unroll
     for (int k = 0; k < PPT; k++) {
         if (hit & (1 << k)) {
+            if (INTERP == 1) { // bilinear: packed-pair sampler straight on the packed pixel
+                if constexpr (sizeof(T) == 1) {
+                    aw[k] = mc_interp_bl_packed<T>(bimg, P.b_width, P.b_height, (float) dxs[k], (float) dys[k], P.mix, aw[k], P.b_alpha);
+                } else {
+                    uint2 o = mc_interp_bl_packed<T>(bimg, P.b_width, P.b_height, (float) dxs[k], (float) dys[k], P.mix,
+                                                     make_uint2(aw[2 * k], aw[2 * k + 1]), P.b_alpha);
+                    aw[2 * k] = o.x, aw[2 * k + 1] = o.y;
+                }
+                continue;
+            }
             uint32_t d[4];
             if (sizeof(T) == 1) {
                 d[0] = aw[k] & 0xff, d[1] = (aw[k] >> 8) & 0xff, d[2] = (aw[k] >> 16) & 0xff, d[3] = aw[k] >> 24;
