@@ -122,46 +122,56 @@ template <typename T, int INTERP> __global__ void __launch_bounds__(256) k_affin
     const int b = blockIdx.z;
     const AffineParams &P = K.p;
     const AffineRow R = mc_affine_row(P, i);
-    if (mc_affine_reject(P, R, j, PPT))
-        return;
     double dxs[PPT], dys[PPT];
-    int hit = 0;
-#pragma unroll
-    for (int k = 0; k < PPT; k++) {
-        mc_affine_map(P, R, j + k, dxs[k], dys[k]);
-        hit |= mc_affine_inside(P, dxs[k], dys[k]) ? (1 << k) : 0;
-    }
-    if (!hit)
+    // x of pixel j + k = (lower_x + j) + k: the reference steps x by ++ from lower_x (:361-363), so both
+    // are exact for the integer / half-integer origins it produces
+    const double x0 = P.lower_x + (double) j;
+    mc_affine_map_x(P, R, x0, dxs[0], dys[0]);
+    mc_affine_map_x(P, R, x0 + (double) (PPT - 1), dxs[PPT - 1], dys[PPT - 1]);
+    if (mc_affine_reject2(P, dxs[0], dys[0], dxs[PPT - 1], dys[PPT - 1]))
         return;
+#pragma unroll
+    for (int k = 1; k < PPT - 1; k++)
+        mc_affine_map_x(P, R, x0 + (double) k, dxs[k], dys[k]);
+    // dx(j), dy(j) are monotone along a row, so a group whose two end pixels are inside B is inside
+    // as a whole: the interior of the rectangle (nearly all covered groups) skips the per-pixel tests
+    // and runs the PPT samplers without branches between them.
+    const bool all = mc_affine_inside(P, dxs[0], dys[0]) && mc_affine_inside(P, dxs[PPT - 1], dys[PPT - 1]);
     T *q = reinterpret_cast<T *>(K.a_image + b * K.a_bs) + ((size_t) i * K.a_width + j) * 4;
     const T *bimg = reinterpret_cast<const T *>(K.b_image + b * K.b_bs);
     asm volatile("" : "+l"(bimg)); // keep the batch base in registers: do not re-derive it per pixel
-    uint4 a = ld16(q);
-    uint32_t aw[4] = {a.x, a.y, a.z, a.w};
+    uint32_t aw[4];
+    if (all) {
+        uint4 a = ld16(q);
+        aw[0] = a.x, aw[1] = a.y, aw[2] = a.z, aw[3] = a.w;
 #pragma unroll
-    for (int k = 0; k < PPT; k++) {
-        if (hit & (1 << k)) {
-            if (INTERP == 1) { // bilinear: packed-pair sampler straight on the packed pixel
+        for (int k = 0; k < PPT; k++) {
+            if constexpr (sizeof(T) == 1) {
+                aw[k] = mc_affine_sample_packed<T, INTERP>(P, bimg, dxs[k], dys[k], aw[k]);
+            } else {
+                uint2 o = mc_affine_sample_packed<T, INTERP>(P, bimg, dxs[k], dys[k], make_uint2(aw[2 * k], aw[2 * k + 1]));
+                aw[2 * k] = o.x, aw[2 * k + 1] = o.y;
+            }
+        }
+    } else {
+        int hit = 0;
+#pragma unroll
+        for (int k = 0; k < PPT; k++)
+            hit |= mc_affine_inside(P, dxs[k], dys[k]) ? (1 << k) : 0;
+        if (!hit)
+            return;
+        uint4 a = ld16(q);
+        aw[0] = a.x, aw[1] = a.y, aw[2] = a.z, aw[3] = a.w;
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+            if (hit & (1 << k)) {
                 if constexpr (sizeof(T) == 1) {
-                    aw[k] = mc_interp_bl_packed<T>(bimg, P.b_width, P.b_height, (float) dxs[k], (float) dys[k], P.mix, aw[k], P.b_alpha);
+                    aw[k] = mc_affine_sample_packed<T, INTERP>(P, bimg, dxs[k], dys[k], aw[k]);
                 } else {
-                    uint2 o = mc_interp_bl_packed<T>(bimg, P.b_width, P.b_height, (float) dxs[k], (float) dys[k], P.mix,
-                                                     make_uint2(aw[2 * k], aw[2 * k + 1]), P.b_alpha);
+                    uint2 o = mc_affine_sample_packed<T, INTERP>(P, bimg, dxs[k], dys[k], make_uint2(aw[2 * k], aw[2 * k + 1]));
                     aw[2 * k] = o.x, aw[2 * k + 1] = o.y;
                 }
-                continue;
             }
-            uint32_t d[4];
-            if (sizeof(T) == 1) {
-                d[0] = aw[k] & 0xff, d[1] = (aw[k] >> 8) & 0xff, d[2] = (aw[k] >> 16) & 0xff, d[3] = aw[k] >> 24;
-            } else {
-                d[0] = aw[2 * k] & 0xffff, d[1] = aw[2 * k] >> 16, d[2] = aw[2 * k + 1] & 0xffff, d[3] = aw[2 * k + 1] >> 16;
-            }
-            mc_affine_sample<T, INTERP>(P, bimg, dxs[k], dys[k], d);
-            if (sizeof(T) == 1)
-                aw[k] = d[0] | (d[1] << 8) | (d[2] << 16) | (d[3] << 24);
-            else
-                aw[2 * k] = d[0] | (d[1] << 16), aw[2 * k + 1] = d[2] | (d[3] << 16);
         }
     }
     *reinterpret_cast<uint4 *>(q) = make_uint4(aw[0], aw[1], aw[2], aw[3]);

@@ -156,17 +156,39 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
         } else if (code == 2) {
             const AffineParams &P = op.a.ap;
             const AffineRow R = mc_affine_row(P, r);
-            if (mc_affine_reject(P, R, col0, 8))
+            const double x0 = P.lower_x + (double) col0; // + k below: see k_affine_rows
+            double ax, ay, bx, by;
+            mc_affine_map_x(P, R, x0, ax, ay);
+            mc_affine_map_x(P, R, x0 + 7.0, bx, by);
+            if (mc_affine_reject2(P, ax, ay, bx, by))
                 continue;
             const uint8_t *bimg = op.a.b_image + b * op.a.b_bs;
+            asm volatile("" : "+l"(bimg)); // keep the batch base in registers
+            // both end pixels inside B => the whole group is (monotone mapping): no per-pixel tests
+            if (mc_affine_inside(P, ax, ay) && mc_affine_inside(P, bx, by)) {
 #pragma unroll
-            for (int k = 0; k < 8; k++) {
-                double dx, dy;
-                mc_affine_map(P, R, col0 + k, dx, dy);
-                if (mc_affine_inside(P, dx, dy)) {
-                    uint32_t d[4] = {rgba[k] & 0xff, (rgba[k] >> 8) & 0xff, (rgba[k] >> 16) & 0xff, rgba[k] >> 24};
-                    mc_affine_sample<uint8_t, ONLY_BL ? 1 : -1>(P, bimg, dx, dy, d);
-                    rgba[k] = d[0] | (d[1] << 8) | (d[2] << 16) | (d[3] << 24);
+                for (int k = 0; k < 8; k++) {
+                    double dx = ax, dy = ay;
+                    if (k == 7)
+                        dx = bx, dy = by;
+                    else if (k > 0)
+                        mc_affine_map_x(P, R, x0 + (double) k, dx, dy);
+                    if (ONLY_BL)
+                        rgba[k] = mc_affine_sample_packed<uint8_t, 1>(P, bimg, dx, dy, rgba[k]);
+                    else
+                        rgba[k] = mc_affine_sample_packed_rt<uint8_t>(P, bimg, dx, dy, rgba[k]);
+                }
+            } else {
+#pragma unroll 1
+                for (int k = 0; k < 8; k++) {
+                    double dx, dy;
+                    mc_affine_map_x(P, R, x0 + (double) k, dx, dy);
+                    if (mc_affine_inside(P, dx, dy)) {
+                        if (ONLY_BL)
+                            rgba[k] = mc_affine_sample_packed<uint8_t, 1>(P, bimg, dx, dy, rgba[k]);
+                        else
+                            rgba[k] = mc_affine_sample_packed_rt<uint8_t>(P, bimg, dx, dy, rgba[k]);
+                    }
                 }
             }
         } else if (code == 3) { // transition_luma.c:452-463, progressive
