@@ -89,6 +89,10 @@ mltcuda_event *mltcuda_event_create(void);
 void mltcuda_event_destroy(mltcuda_event *ev);
 int mltcuda_event_record(mltcuda_ctx *ctx, mltcuda_event *ev);
 int mltcuda_event_sync(mltcuda_event *ev);
+/* Work submitted to `ctx` after this call starts only once `ev` (recorded on any context of the
+ * same process) has completed: the device-side ordering between the streams of two worker threads
+ * (e.g. a frame produced on one worker's context and consumed on another's). */
+int mltcuda_ctx_wait_event(mltcuda_ctx *ctx, mltcuda_event *ev);
 float mltcuda_event_elapsed_ms(mltcuda_event *start, mltcuda_event *stop);
 
 /* ------------------------------------------------------------------------------------------ */

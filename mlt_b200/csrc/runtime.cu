@@ -218,6 +218,15 @@ int mltcuda_event_record(mltcuda_ctx *ctx, mltcuda_event *ev)
     return 0;
 }
 
+int mltcuda_ctx_wait_event(mltcuda_ctx *ctx, mltcuda_event *ev)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!ev, "null event");
+    MC_CHECK(cudaStreamWaitEvent(ctx->stream, ev->ev, 0));
+    return 0;
+}
+
 int mltcuda_event_sync(mltcuda_event *ev)
 {
     MC_CHECK(cudaEventSynchronize(ev->ev));
