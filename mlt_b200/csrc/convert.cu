@@ -60,8 +60,7 @@ __global__ void __launch_bounds__(256) k_yuv422_rgba_v(CvtParams P)
     uint32_t o[8];
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        uint32_t a0 = (a[k >> 1] >> ((k & 1) * 16)) & 0xff, a1 = (a[k >> 1] >> ((k & 1) * 16 + 8)) & 0xff;
-        mc_yuyv_to_rgba2(w[k], a0, a1, o[2 * k], o[2 * k + 1]);
+        mc_yuyv_to_rgba2w(w[k], a[k >> 1], (k & 1) * 2, (k & 1) * 2 + 1, o[2 * k], o[2 * k + 1]);
     }
     if (px >= 8) {
         reinterpret_cast<uint4 *>(d)[0] = make_uint4(o[0], o[1], o[2], o[3]);

@@ -139,11 +139,8 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
         } else if (code == 4 || code == 5) {
             if (code == 4) { // filter_imageconvert.c:58-111
 #pragma unroll
-                for (int k = 0; k < 4; k++) {
-                    uint32_t a0 = has_alpha ? (al[k >> 1] >> ((k & 1) * 16)) & 0xff : 0xff;
-                    uint32_t a1 = has_alpha ? (al[k >> 1] >> ((k & 1) * 16 + 8)) & 0xff : 0xff;
-                    mc_yuyv_to_rgba2(yuv[k], a0, a1, rgba[2 * k], rgba[2 * k + 1]);
-                }
+                for (int k = 0; k < 4; k++) // al[] is all 0xff while the frame has no alpha plane
+                    mc_yuyv_to_rgba2w(yuv[k], al[k >> 1], (k & 1) * 2, (k & 1) * 2 + 1, rgba[2 * k], rgba[2 * k + 1]);
                 fmt = MLTCUDA_FMT_RGBA, has_alpha = 0; // convert_image clears the alpha plane (:475-477)
             } else { // filter_imageconvert.c:144-184: creates the alpha plane
 #pragma unroll
