@@ -108,6 +108,26 @@ template <bool DISSOLVE> __global__ void __launch_bounds__(256) k_luma_yuv422(Lu
     uint8_t *as = K.alpha_src ? K.alpha_src + b * K.as_bs + (DISSOLVE ? (size_t) i * K.width_src : (size_t) ordinal * K.width_src)
                               : nullptr;
     uint32_t o[4];
+    if (!DISSOLVE && !translucent && jlo == j0 && jhi == j0 + 8) {
+        // opaque wipe on a whole group (:452-463): integer path without per-pixel predicates
+        const uint32_t step = (uint32_t) ((1 << 16) * fpos);
+        uint32_t lum[8];
+        if (K.x_diff == 65536) { // map as wide as the frame: 8 consecutive entries = 16 bytes
+            uint32_t lw[4];
+            fetch16((uintptr_t) (l + j0), (uintptr_t) l, (uintptr_t) (l + K.luma_width), lw);
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+                lum[k] = (k & 1) ? lw[k >> 1] >> 16 : lw[k >> 1] & 0xffff;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+                lum[k] = __ldg(l + (((uint32_t) (j0 + k) * (uint32_t) K.x_diff) >> 16));
+        }
+        mc_luma_wipe_group8(s, d, lum, step, K.i_softness, K.soft_magic);
+        o[0] = d[0], o[1] = d[1], o[2] = d[2], o[3] = d[3];
+        *dptr = make_uint4(o[0], o[1], o[2], o[3]);
+        return;
+    }
 #pragma unroll
     for (int k = 0; k < 8; k++) {
         int j = j0 + k;

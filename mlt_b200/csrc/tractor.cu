@@ -197,6 +197,14 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
             fetch16((uintptr_t) srow + 2 * col0, (uintptr_t) srow + 2 * col0,
                     (uintptr_t) srow + 2 * (col0 + 8 > L.width_src ? L.width_src : col0 + 8), s);
             const uint16_t *l = L.map + (long) ((r * L.y_diff) >> 16) * L.luma_width;
+            if (col0 + 8 <= L.width_src) {
+                uint32_t lum[8];
+#pragma unroll
+                for (int k = 0; k < 8; k++)
+                    lum[k] = __ldg(l + (((uint32_t) (col0 + k) * (uint32_t) L.x_diff) >> 16));
+                mc_luma_wipe_group8(s, yuv, lum, L.step, L.i_softness, L.soft_magic);
+                continue;
+            }
 #pragma unroll
             for (int k = 0; k < 8; k++) {
                 int j = col0 + k;

@@ -45,14 +45,17 @@ def main():
     d_y0, d_y1 = ctx.alloc(B * yb), ctx.alloc(B * yb)
     d_r0, d_r1 = ctx.alloc(B * rb), ctx.alloc(B * rb)
     d_a0, d_a1 = ctx.alloc(B * ab_), ctx.alloc(B * ab_)
-    d_map = ctx.alloc(NPX * 2)
+    # luma map: a horizontal ramp 0..65535 like demo/luma1.pgm (a wipe); with pos 0.4 / softness 0.2
+    # about a fifth of every row lies inside the soft band (smoothstep polynomial), the rest is 0 / 1
+    import numpy as np
+    ramp = np.tile((np.arange(W, dtype=np.uint64) * 65535 // (W - 1)).astype(np.uint16), H)
+    d_map = ctx.put(ramp.view(np.uint8))
     abi.check(lib.mltcuda_noise(ctx.h, d_y0.ptr, W, H, 1, B, yb))
     abi.check(lib.mltcuda_noise(ctx.h, d_y1.ptr, W, H, 1001, B, yb))
     abi.check(lib.mltcuda_noise(ctx.h, d_r0.ptr, W * 2, H, 2001, B, rb))
     abi.check(lib.mltcuda_noise(ctx.h, d_r1.ptr, W * 2, H, 3001, B, rb))
     abi.check(lib.mltcuda_noise(ctx.h, d_a0.ptr, W // 2, H, 4001, B, ab_))
     abi.check(lib.mltcuda_noise(ctx.h, d_a1.ptr, W // 2, H, 5001, B, ab_))
-    abi.check(lib.mltcuda_noise(ctx.h, d_map.ptr, W, H, 6001, 1, 0))
     ctx.sync()
     ev0, ev1 = lib.mltcuda_event_create(), lib.mltcuda_event_create()
     lines = []
