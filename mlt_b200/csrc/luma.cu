@@ -203,7 +203,7 @@ template <bool DISSOLVE> __global__ void __launch_bounds__(256) k_luma_yuv422(Lu
 
 // luma_composite_rgba32/_rgba64 (:475-723) and dissolve_slice_rgba32/_rgba64 (:192-265).
 // T = uint8_t: 4 px per thread; uint16_t: 2 px per thread (16 bytes of A either way).
-template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256) k_luma_rgba(LumaK K)
+template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256, 6) k_luma_rgba(LumaK K)
 {
     constexpr int PPT = sizeof(T) == 1 ? 4 : 2;
     const float maxv = PxTraits<T>::maxv;
@@ -211,10 +211,23 @@ template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256) k_lu
     const int w = K.width_src, h = K.height_src;
     const long long npx = (long long) w * h;
     const long long cpf = (npx + PPT - 1) / PPT;
-    // grid = (groups of a frame, 1, frame); a frame has < 2^31 pixels, so 32-bit index math
-    const unsigned gid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (gid >= (unsigned) cpf)
-        return;
+    // K.cpr > 0 (row width a multiple of PPT): 2-D CTAs of 32 groups x 8 rows, no division.
+    // Otherwise grid = (groups of a frame, 1, frame); a frame has < 2^31 pixels: 32-bit index math.
+    unsigned gid;
+    int i, j;
+    if (K.cpr > 0) {
+        const int g = blockIdx.x * 32 + threadIdx.x;
+        i = blockIdx.y * 8 + threadIdx.y;
+        if (g >= K.cpr || i >= h)
+            return;
+        j = g * PPT;
+        gid = (unsigned) i * (unsigned) K.cpr + (unsigned) g;
+    } else {
+        gid = blockIdx.x * blockDim.x + threadIdx.x;
+        if (gid >= (unsigned) cpf)
+            return;
+        i = (int) (gid * PPT / (unsigned) w), j = (int) (gid * PPT - (unsigned) i * (unsigned) w);
+    }
     const int b = blockIdx.z;
     const unsigned p0 = gid * PPT;
     const int translucent = K.flag ? *K.flag : K.forced;
@@ -244,10 +257,58 @@ template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256) k_lu
                 qv[k][c] = ok ? q[4 * k + c] : 0, pv[k][c] = ok ? p[4 * k + c] : 0;
             }
     }
-    int i = (int) (p0 / (unsigned) w), j = (int) (p0 - (unsigned) i * (unsigned) w);
     int field = 0, y_off = 0, ordinal = 0;
     const uint16_t *lrow = nullptr;
     float fpos = 0.f;
+    if (!DISSOLVE && !translucent && full && j + PPT <= w) {
+        // opaque wipe, whole group inside one row (:576-590, :693-707): RGB mixed in integers, alpha kept
+        luma_row_info(K, i, field, y_off, ordinal);
+        fpos = field ? K.field_pos1 : K.field_pos0;
+        lrow = K.map + (long) (y_off >> 16) * (K.luma_width * K.field_count);
+        const uint32_t step = (uint32_t) ((1 << 16) * fpos);
+        uint32_t x[PPT], v[PPT];
+        bool band = false;
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+            x[k] = step - __ldg(lrow + (((uint32_t) (j + k) * (uint32_t) K.x_diff) >> 16));
+            band |= x[k] < K.i_softness;
+        }
+        uint4 a = ld16(q), s = ldg16(p);
+        uint32_t aw[4] = {a.x, a.y, a.z, a.w}, sw[4] = {s.x, s.y, s.z, s.w};
+        if (!band) { // every pixel fully A or fully B (alpha stays A's)
+#pragma unroll
+            for (int k = 0; k < PPT; k++) {
+                if ((int32_t) x[k] >= 0) {
+                    if (sizeof(T) == 1)
+                        aw[k] = __byte_perm(sw[k], aw[k], 0x7210);
+                    else
+                        aw[2 * k] = sw[2 * k], aw[2 * k + 1] = __byte_perm(sw[2 * k + 1], aw[2 * k + 1], 0x7610);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < PPT; k++) {
+                const uint32_t t = mc_div_by(x[k] << 16, K.i_softness, K.soft_magic);
+                const uint32_t poly = (((t * t) >> 16) * ((3u << 16) - (2 * t))) >> 16;
+                v[k] = x[k] < K.i_softness ? poly : ((int32_t) x[k] < 0 ? 0u : 0x10000u);
+                const uint32_t iv = 65536u - v[k];
+                if (sizeof(T) == 1) { // byte 2 of each sum is the mixed channel
+                    const uint32_t c0 = (sw[k] & 0xff) * v[k] + (aw[k] & 0xff) * iv;
+                    const uint32_t c1 = __byte_perm(sw[k], 0, 0x4441) * v[k] + __byte_perm(aw[k], 0, 0x4441) * iv;
+                    const uint32_t c2 = __byte_perm(sw[k], 0, 0x4442) * v[k] + __byte_perm(aw[k], 0, 0x4442) * iv;
+                    aw[k] = __byte_perm(__byte_perm(c0, c1, 0x0062), __byte_perm(c2, aw[k], 0x0072), 0x5410);
+                } else { // upper half of each sum
+                    const uint32_t c0 = (sw[2 * k] & 0xffff) * v[k] + (aw[2 * k] & 0xffff) * iv;
+                    const uint32_t c1 = (sw[2 * k] >> 16) * v[k] + (aw[2 * k] >> 16) * iv;
+                    const uint32_t c2 = (sw[2 * k + 1] & 0xffff) * v[k] + (aw[2 * k + 1] & 0xffff) * iv;
+                    aw[2 * k] = __byte_perm(c0, c1, 0x7632);
+                    aw[2 * k + 1] = __byte_perm(c2, aw[2 * k + 1], 0x7632);
+                }
+            }
+        }
+        *reinterpret_cast<uint4 *>(q) = make_uint4(aw[0], aw[1], aw[2], aw[3]);
+        return;
+    }
 #pragma unroll
     for (int k = 0; k < PPT; k++) {
         if (p0 + k < npx) {
@@ -447,17 +508,22 @@ extern "C" int mltcuda_luma(mltcuda_ctx *ctx, const mltcuda_luma_desc *d)
         const int ppt = fmt == MLTCUDA_FMT_RGBA ? 4 : 2;
         long long per_frame = ((long long) K.width_src * K.height_src + ppt - 1) / ppt;
         MC_BADARG(per_frame * ppt >= (1ll << 31) || K.batch > 65535, "frame too large / too many frames for one launch");
-        dim3 blocks(mc_blocks(per_frame, 256), 1, K.batch);
+        dim3 blocks(mc_blocks(per_frame, 256), 1, K.batch), threads(256, 1, 1);
+        K.cpr = 0;
+        if (K.width_src % ppt == 0 && (K.height_src + 7) / 8 <= 65535) {
+            K.cpr = K.width_src / ppt;
+            blocks = dim3((K.cpr + 31) / 32, (K.height_src + 7) / 8, K.batch), threads = dim3(32, 8, 1);
+        }
         if (fmt == MLTCUDA_FMT_RGBA) {
             if (dissolve)
-                k_luma_rgba<uint8_t, true><<<blocks, 256, 0, ctx->stream>>>(K);
+                k_luma_rgba<uint8_t, true><<<blocks, threads, 0, ctx->stream>>>(K);
             else
-                k_luma_rgba<uint8_t, false><<<blocks, 256, 0, ctx->stream>>>(K);
+                k_luma_rgba<uint8_t, false><<<blocks, threads, 0, ctx->stream>>>(K);
         } else {
             if (dissolve)
-                k_luma_rgba<uint16_t, true><<<blocks, 256, 0, ctx->stream>>>(K);
+                k_luma_rgba<uint16_t, true><<<blocks, threads, 0, ctx->stream>>>(K);
             else
-                k_luma_rgba<uint16_t, false><<<blocks, 256, 0, ctx->stream>>>(K);
+                k_luma_rgba<uint16_t, false><<<blocks, threads, 0, ctx->stream>>>(K);
         }
         rc = mc_after_launch(ctx, "k_luma_rgba");
     }
