@@ -162,8 +162,26 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
             const uint8_t *bimg = op.a.b_image + b * op.a.b_bs;
             asm volatile("" : "+l"(bimg)); // keep the batch base in registers
             // both end pixels inside B => the whole group is (monotone mapping): no per-pixel tests
-            if (mc_affine_inside(P, ax, ay) && mc_affine_inside(P, bx, by)) {
+            if (ONLY_BL && mc_affine_inside(P, ax, ay) && mc_affine_inside(P, bx, by)) {
+                // bilinear, whole group inside: taps of four pixels in flight before any blend
 #pragma unroll
+                for (int h4 = 0; h4 < 8; h4 += 4) {
+                    BlTaps<uint8_t> taps[4];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        double dx = ax, dy = ay;
+                        if (h4 + k == 7)
+                            dx = bx, dy = by;
+                        else if (h4 + k > 0)
+                            mc_affine_map_x(P, R, x0 + (double) (h4 + k), dx, dy);
+                        taps[k] = mc_bl_fetch<uint8_t>(bimg, P.b_width, P.b_height, (float) dx, (float) dy);
+                    }
+#pragma unroll
+                    for (int k = 0; k < 4; k++)
+                        rgba[h4 + k] = mc_bl_blend<uint8_t>(taps[k], P.mix, rgba[h4 + k], P.b_alpha);
+                }
+            } else if (!ONLY_BL && mc_affine_inside(P, ax, ay) && mc_affine_inside(P, bx, by)) {
+#pragma unroll 1
                 for (int k = 0; k < 8; k++) {
                     double dx = ax, dy = ay;
                     if (k == 7)
