@@ -82,8 +82,12 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
     // 2-D CTA: 32 groups (256 px) x 8 rows -- no div/mod, and the B taps of neighbouring rows share L1
     const int c = blockIdx.x * 32 + threadIdx.x;
     const int r = blockIdx.y * 8 + threadIdx.y;
-    if (c >= (K.width >> 3) || r >= K.height)
+    // blockDim.x == 32: a warp is 32 consecutive groups (256 px) of one row
+    const bool valid = c < (K.width >> 3) && r < K.height;
+    const bool fullwarp = __ballot_sync(0xffffffffu, valid) == 0xffffffffu;
+    if (!valid)
         return;
+    __shared__ uint32_t s_xpose[8][256]; // per-warp staging for the transposed affine pass
     const int b = blockIdx.z;
     const int col0 = c * 8;
     const size_t pix0 = (size_t) r * K.width + col0;
@@ -153,6 +157,54 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
         } else if (code == 2) {
             const AffineParams &P = op.a.ap;
             const AffineRow R = mc_affine_row(P, r);
+            if (ONLY_BL && fullwarp) {
+                // Transposed pass.  With 8 consecutive pixels per thread the 32 lanes of a tap load
+                // are 8 destination pixels apart -- up to 32 different L1 lines per LDG, which made the
+                // taps the latency AND the L1-wavefront limit of the kernel (profiles/r1f).  Here the
+                // warp's 256 pixels go through shared memory so that lane i samples pixels i, i+32, ...:
+                // one tap load then touches 2-4 adjacent lines.  Same per-pixel arithmetic as below.
+                __syncwarp();
+                const int wcol0 = blockIdx.x * 256;
+                const double xw0 = P.lower_x + (double) wcol0;
+                double ax, ay, bx, by;
+                mc_affine_map_x(P, R, xw0, ax, ay);
+                mc_affine_map_x(P, R, xw0 + 255.0, bx, by);
+                if (mc_affine_reject2(P, ax, ay, bx, by))
+                    continue; // warp-uniform
+                const bool all = mc_affine_inside(P, ax, ay) && mc_affine_inside(P, bx, by);
+                const uint8_t *bimg = op.a.b_image + b * op.a.b_bs;
+                asm volatile("" : "+l"(bimg));
+                uint32_t *sm = s_xpose[threadIdx.y];
+                reinterpret_cast<uint4 *>(sm)[2 * threadIdx.x] = make_uint4(rgba[0], rgba[1], rgba[2], rgba[3]);
+                reinterpret_cast<uint4 *>(sm)[2 * threadIdx.x + 1] = make_uint4(rgba[4], rgba[5], rgba[6], rgba[7]);
+                __syncwarp();
+                const double xl = xw0 + (double) threadIdx.x;
+#pragma unroll
+                for (int h4 = 0; h4 < 8; h4 += 4) {
+                    BlTaps<uint8_t> taps[4];
+                    bool in[4];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        double dx, dy;
+                        mc_affine_map_x(P, R, xl + (double) (32 * (h4 + k)), dx, dy);
+                        in[k] = all || mc_affine_inside(P, dx, dy);
+                        if (in[k])
+                            taps[k] = mc_bl_fetch<uint8_t>(bimg, P.b_width, P.b_height, (float) dx, (float) dy);
+                    }
+#pragma unroll
+                    for (int k = 0; k < 4; k++)
+                        if (in[k]) {
+                            const int p = 32 * (h4 + k) + threadIdx.x;
+                            sm[p] = mc_bl_blend<uint8_t>(taps[k], P.mix, sm[p], P.b_alpha);
+                        }
+                }
+                __syncwarp();
+                const uint4 q0 = reinterpret_cast<const uint4 *>(sm)[2 * threadIdx.x];
+                const uint4 q1 = reinterpret_cast<const uint4 *>(sm)[2 * threadIdx.x + 1];
+                rgba[0] = q0.x, rgba[1] = q0.y, rgba[2] = q0.z, rgba[3] = q0.w;
+                rgba[4] = q1.x, rgba[5] = q1.y, rgba[6] = q1.z, rgba[7] = q1.w;
+                continue;
+            }
             const double x0 = P.lower_x + (double) col0; // + k below: see k_affine_rows
             double ax, ay, bx, by;
             mc_affine_map_x(P, R, x0, ax, ay);
