@@ -52,3 +52,17 @@ int main(void){printf("%zu %zu %zu %zu %zu %zu %zu\n", sizeof(mltcuda_convert_de
     mirror = [abi.ConvertDesc, abi.CompositeDesc, abi.CompositeGeometry, abi.LumaDesc, abi.AffineDesc, abi.TractorOp,
               abi.TractorDesc]
     assert sizes == [C.sizeof(m) for m in mirror]
+
+
+def test_no_contracted_pair_fma():
+    """ptxas contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even under --fmad=false; the
+    samplers must keep the reference's two roundings, so no kernel of the library may contain FFMA2."""
+    import shutil
+    import subprocess
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    so = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "mlt_b200", "lib", "libmltcuda_rt.so")
+    sass = subprocess.run([cuobjdump, "-sass", so], capture_output=True, text=True, check=True).stdout
+    assert "FADD2" in sass and "FMUL2" in sass, "packed fp32 pair ops missing: wrong build?"
+    assert "FFMA2" not in sass, "a packed multiply-add pair was contracted: results would differ from the reference"
