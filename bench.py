@@ -403,8 +403,8 @@ def run_ours(args, dist):
                 "config": {"workload": "cfg4_uhd_2160p_60_4track", "frames_per_step": F, "width": W, "height": H,
                            "launches_per_frame": 1, "worker_streams": len(workers), "l2": "inputs larger than L2 (step working set ~1.6 GB)",
                            "parallelism": f"frame-sharded x{dist.world}, no collective"},
-                "e2e": {"value": round(e2e_val, 1), "unit": "frames/s", "h2d_bytes_per_step": F * (fb + b1b + b3b),
-                        "d2h_bytes_per_step": F * fb, "steps": e2e_steps, "matches_device_leg": e2e_ok},
+                "e2e": {"value": round(e2e_val, 1), "unit": "frames/s", "h2d_bytes_per_step": dist.world * F * (fb + b1b + b3b),
+                        "d2h_bytes_per_step": dist.world * F * fb, "steps": e2e_steps, "matches_device_leg": e2e_ok},
                 "gpu_launches": total_launches, "roofline": roofline, "clocks": clk}
         if cpu:
             line["cpu_baseline"] = cpu

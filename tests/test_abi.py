@@ -3,6 +3,8 @@ points include/mltcuda.h declares (no compute calls: there is no GPU here)."""
 import os
 import re
 
+import pytest
+
 from mlt_b200 import abi
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
