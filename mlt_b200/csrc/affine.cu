@@ -202,8 +202,17 @@ int mc_fill_affine_params(AffineParams &p, const mltcuda_affine_desc *d)
     p.b_width = d->b_width, p.b_height = d->b_height, p.b_alpha = d->b_alpha, p.interp = d->interp;
     // The reference samplers read a 2x2 (BL) / 4x4 (BC) footprint clamped to the image; smaller
     // images make it read out of bounds.  Refuse instead of faulting.
+    // tap offsets are 32-bit unsigned byte offsets (mc_tap2): the reference caps B at 16000 x 16000
+    // (MLT_AFFINE_MAX_DIMENSION, transition_affine.c:32), 2 GiB in rgba64
+    if ((unsigned long long) d->b_width * (unsigned long long) d->b_height * (d->format == MLTCUDA_FMT_RGBA64 ? 8ull : 4ull) >= (1ull << 32)) {
+        mltcuda_set_error("affine: B image %dx%d is 4 GiB or more", d->b_width, d->b_height);
+        return MLTCUDA_E_BADARG;
+    }
+    // ... except bilinear on a 1-wide / 1-high B, which the reference does produce (App. B-3) and
+    // whose result is well defined (mc_interp_bl): served by the generic kernel with clamped taps.
+    p.degenerate = d->interp == MLTCUDA_INTERP_BL && d->b_width >= 1 && d->b_height >= 1 && (d->b_width < 2 || d->b_height < 2);
     int need = d->interp == MLTCUDA_INTERP_BL ? 2 : d->interp == MLTCUDA_INTERP_BC ? 4 : 1;
-    if (d->b_width < need || d->b_height < need) {
+    if (!p.degenerate && (d->b_width < need || d->b_height < need)) {
         mltcuda_set_error("affine: B image %dx%d smaller than the %dx%d sampler footprint", d->b_width, d->b_height, need, need);
         return MLTCUDA_E_BADARG;
     }
@@ -230,7 +239,7 @@ extern "C" int mltcuda_affine(mltcuda_ctx *ctx, const mltcuda_affine_desc *d)
         MC_BADARG(!K.a_bs, "batch > 1 needs a_bstride");
     const int ppt = d->format == MLTCUDA_FMT_RGBA ? 4 : 2;
     long long total = (((long long) d->a_width * d->a_height + ppt - 1) / ppt) * K.batch;
-    const bool rows_ok = d->a_width % ppt == 0 && ((uintptr_t) d->a_image & 15) == 0 && (K.a_bs & 15) == 0
+    const bool rows_ok = !K.p.degenerate && d->a_width % ppt == 0 && ((uintptr_t) d->a_image & 15) == 0 && (K.a_bs & 15) == 0
                          && (d->a_height + 7) / 8 <= 65535 && K.batch <= 65535;
     if (rows_ok && d->format == MLTCUDA_FMT_RGBA)
         launch_affine_rows<uint8_t>(K, d->interp, ctx->stream);

@@ -362,6 +362,11 @@ extern "C" int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d)
             MC_BADARG(!o.u.affine.b_image, "null B image");
             if (int e = mc_fill_affine_params(t.a.ap, &o.u.affine))
                 return e;
+            if (t.a.ap.degenerate) {
+                mltcuda_set_error("fused tractor pass: affine B image %dx%d below the 2x2 footprint; run the ops unfused",
+                                  o.u.affine.b_width, o.u.affine.b_height);
+                return MLTCUDA_E_UNSUPPORTED;
+            }
             t.a.b_image = (const uint8_t *) o.u.affine.b_image, t.a.b_bs = o.u.affine.b_bstride;
             only_bl = only_bl && t.a.ap.interp == MLTCUDA_INTERP_BL;
         } else if (o.kind == MLTCUDA_TOP_LUMA) {

@@ -115,6 +115,13 @@ EXACT = [
      A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=0/0:100%x100%:50%"]),
     ("imageconvert_rgb_out", "rgb", [10],
      A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=25%/25%:50%x50%:50%"]),
+    # stock wrapper filters that create the path's transitions BY NAME
+    # (mlt_factory_transition(profile, "composite" / "luma")) pick up the CUDA services through the
+    # create-request override -- core/filter_watermark.c, core/filter_luma.c
+    ("wrapper_watermark", "yuv422", [10],
+     A + ["-attach", "watermark:colour:0x3060c0a0", "composite.geometry=10%/10%:50%x50%:70%"]),
+    ("wrapper_luma_filter", "yuv422", [13, 27],
+     A + ["-attach", f"luma:{mltenv.LUMA_PGM}", "cycle=10", "duration=6"]),
     ("imageconvert_yuv420p_out", "yuv420p", [10],
      A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=25%/25%:50%x50%:50%"]),
 ]
@@ -152,6 +159,9 @@ CLOSE = [
     ("affine_colour_b_alpha", "rgba", [30], "bilinear",
      A + ["-track", "colour:0x3060c0a0", "out=249", "-transition", "affine", "rect=20%/20%:50%x50%:90%", "rotate_x=0.5",
           "b_alpha=1", "halign=centre", "valign=middle", "a_track=0", "b_track=1"]),
+    # f3: plus/filter_affine.c instantiates the "affine" transition by name over a colour background
+    ("wrapper_affine_filter", "rgba", [30], "bilinear",
+     A + ["-attach", "affine", "transition.rect=10%/10%:60%x60%:80%", "transition.fix_rotate_x=15", "background=colour:0x20406080"]),
     ("cfg4_1080p", "yuv422", [0, 37], "bilinear",
      A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=5%/5%:40%x40%:80%", "-track",
                     "colour:0x3060c0a0", "out=599", "-transition", "affine", "a_track=0", "b_track=2",
