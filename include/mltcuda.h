@@ -74,12 +74,21 @@ void mltcuda_free(mltcuda_ctx *ctx, void *dev_ptr);
 /* Pinned host memory for staging. */
 void *mltcuda_host_alloc(size_t bytes);
 void mltcuda_host_free(void *host_ptr);
+/* Recycling pool of pinned buffers for images returned to host code (the replacement of
+ * mlt_pool_alloc / mlt_pool_release for frames this module downloads): thread-safe, exact-size reuse. */
+void *mltcuda_host_pool_alloc(size_t bytes);
+void mltcuda_host_pool_release(void *host_ptr);
 int mltcuda_host_register(void *host_ptr, size_t bytes);
 int mltcuda_host_unregister(void *host_ptr);
 
 /* Async copies on the context stream (cudaMemcpyAsync). */
 int mltcuda_upload(mltcuda_ctx *ctx, void *dst_dev, const void *src_host, size_t bytes);
 int mltcuda_download(mltcuda_ctx *ctx, void *dst_host, const void *src_dev, size_t bytes);
+/* Upload from PAGEABLE host memory -- the mlt_pool_alloc buffers stock producers hand out
+ * (src/framework/mlt_pool.c:277) -- through the context's two pinned staging slots, the caller's
+ * memcpy of one chunk overlapping the DMA of the previous one.  `src_host` may be released when the
+ * call returns; the copy is ordered on the context stream like mltcuda_upload. */
+int mltcuda_upload_staged(mltcuda_ctx *ctx, void *dst_dev, const void *src_host, size_t bytes);
 int mltcuda_copy(mltcuda_ctx *ctx, void *dst_dev, const void *src_dev, size_t bytes);
 int mltcuda_memset(mltcuda_ctx *ctx, void *dst_dev, int value, size_t bytes);
 

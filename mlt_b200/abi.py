@@ -106,6 +106,9 @@ SIGNATURES = {
     "mltcuda_event_record": (C.c_int, [vp, vp]),
     "mltcuda_event_sync": (C.c_int, [vp]),
     "mltcuda_ctx_wait_event": (C.c_int, [vp, vp]),
+    "mltcuda_upload_staged": (C.c_int, [vp, vp, vp, C.c_size_t]),
+    "mltcuda_host_pool_alloc": (vp, [C.c_size_t]),
+    "mltcuda_host_pool_release": (None, [vp]),
     "mltcuda_event_elapsed_ms": (C.c_float, [vp, vp]),
     "mltcuda_convert": (C.c_int, [vp, C.POINTER(ConvertDesc)]),
     "mltcuda_composite": (C.c_int, [vp, C.POINTER(CompositeDesc)]),

@@ -13,7 +13,12 @@ struct mltcuda_ctx
     unsigned long long launches;
     int sm_count;
     uint32_t *noise_tab; // device: skip-ahead tables for the noise producer (lazy)
+    // pinned double-buffered staging for uploads from pageable host memory (mltcuda_upload_staged)
+    void *stage[2];
+    cudaEvent_t stage_done[2];
+    int stage_next;
 };
+#define MLTCUDA_STAGE_BYTES (4u << 20)
 
 struct mltcuda_event
 {

@@ -3,6 +3,9 @@
 // (reference src/framework/mlt_consumer.c:1079-1170) bind to; frames shard by worker, no
 // collective.
 #include "common.cuh"
+#include <mutex>
+#include <vector>
+#include <string.h>
 #include <stdarg.h>
 #include <atomic>
 
@@ -60,6 +63,7 @@ mltcuda_ctx *mltcuda_ctx_create(int device)
     ctx->device = device;
     ctx->launches = 0;
     ctx->noise_tab = nullptr;
+    ctx->stage[0] = ctx->stage[1] = nullptr, ctx->stage_next = 0;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
         mltcuda_set_error("cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError()));
         delete ctx;
@@ -81,6 +85,11 @@ void mltcuda_ctx_destroy(mltcuda_ctx *ctx)
     cudaStreamSynchronize(ctx->stream);
     if (ctx->noise_tab)
         cudaFree(ctx->noise_tab);
+    for (int i = 0; i < 2; i++)
+        if (ctx->stage[i]) {
+            cudaFreeHost(ctx->stage[i]);
+            cudaEventDestroy(ctx->stage_done[i]);
+        }
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -147,6 +156,66 @@ void mltcuda_host_free(void *p)
         cudaFreeHost(p);
 }
 
+// Recycling pool of pinned host buffers for images handed back to host code (a download straight
+// into pinned memory needs no staging copy).  cudaHostAlloc costs milliseconds, frames repeat the
+// same few sizes: freed buffers are kept (exact-size match) up to a cap.
+namespace {
+struct PinnedEntry
+{
+    void *p;
+    size_t bytes;
+    bool busy;
+};
+std::mutex g_pin_lock;
+std::vector<PinnedEntry> g_pinned;
+size_t g_pinned_idle_bytes = 0;
+const size_t PINNED_IDLE_CAP = 4ull << 30;
+} // namespace
+
+void *mltcuda_host_pool_alloc(size_t bytes)
+{
+    if (!bytes)
+        bytes = 1;
+    {
+        std::lock_guard<std::mutex> g(g_pin_lock);
+        for (auto &e : g_pinned)
+            if (!e.busy && e.bytes == bytes) {
+                e.busy = true;
+                g_pinned_idle_bytes -= bytes;
+                return e.p;
+            }
+    }
+    void *p = mltcuda_host_alloc(bytes);
+    if (!p)
+        return nullptr;
+    std::lock_guard<std::mutex> g(g_pin_lock);
+    g_pinned.push_back({p, bytes, true});
+    return p;
+}
+
+void mltcuda_host_pool_release(void *p)
+{
+    if (!p)
+        return;
+    void *to_free = nullptr;
+    {
+        std::lock_guard<std::mutex> g(g_pin_lock);
+        for (size_t i = 0; i < g_pinned.size(); i++)
+            if (g_pinned[i].p == p) {
+                if (g_pinned_idle_bytes + g_pinned[i].bytes > PINNED_IDLE_CAP) {
+                    to_free = p;
+                    g_pinned.erase(g_pinned.begin() + i);
+                } else {
+                    g_pinned[i].busy = false;
+                    g_pinned_idle_bytes += g_pinned[i].bytes;
+                }
+                break;
+            }
+    }
+    if (to_free)
+        cudaFreeHost(to_free);
+}
+
 int mltcuda_host_register(void *p, size_t bytes)
 {
     MC_CHECK(cudaHostRegister(p, bytes, cudaHostRegisterPortable));
@@ -164,6 +233,38 @@ int mltcuda_upload(mltcuda_ctx *ctx, void *dst, const void *src, size_t bytes)
     if (int e = mc_use(ctx))
         return e;
     MC_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return 0;
+}
+
+// Upload from PAGEABLE host memory (the reference's mlt_pool buffers) at PCIe speed: the source is
+// copied by the calling thread into two pinned 4 MiB slots in turn, each followed by an asynchronous
+// DMA on the context stream, so the CPU copy of chunk k+1 overlaps the DMA of chunk k.  A plain
+// cudaMemcpyAsync from pageable memory goes through the driver's own staging buffer, under a
+// process-wide lock: 16 worker threads together reached 3.7 GB/s (tools/melt_bench.py).  The
+// source may be released as soon as the call returns.
+int mltcuda_upload_staged(mltcuda_ctx *ctx, void *dst, const void *src, size_t bytes)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!dst || !src, "null pointer");
+    for (int i = 0; i < 2; i++)
+        if (!ctx->stage[i]) {
+            MC_CHECK(cudaHostAlloc(&ctx->stage[i], MLTCUDA_STAGE_BYTES, cudaHostAllocPortable));
+            MC_CHECK(cudaEventCreateWithFlags(&ctx->stage_done[i], cudaEventDisableTiming));
+            MC_CHECK(cudaEventRecord(ctx->stage_done[i], ctx->stream));
+        }
+    const char *s = (const char *) src;
+    char *d = (char *) dst;
+    while (bytes) {
+        const size_t n = bytes < MLTCUDA_STAGE_BYTES ? bytes : (size_t) MLTCUDA_STAGE_BYTES;
+        const int i = ctx->stage_next;
+        ctx->stage_next ^= 1;
+        MC_CHECK(cudaEventSynchronize(ctx->stage_done[i])); // the slot's previous DMA has left
+        memcpy(ctx->stage[i], s, n);
+        MC_CHECK(cudaMemcpyAsync(d, ctx->stage[i], n, cudaMemcpyHostToDevice, ctx->stream));
+        MC_CHECK(cudaEventRecord(ctx->stage_done[i], ctx->stream));
+        s += n, d += n, bytes -= n;
+    }
     return 0;
 }
 

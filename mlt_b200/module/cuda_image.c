@@ -154,12 +154,12 @@ static cuda_image upload_host_image(mlt_frame frame, mltcuda_ctx *ctx, const uin
     cuda_image ci = cuda_image_new(ctx, format, width, height, alpha != NULL);
     if (!ci)
         return NULL;
-    int rc = mltcuda_upload(ctx, ci->data, image, cuda_format_bytes(format, width, height));
+    /* the source buffers are pageable (mlt_pool) and owned by the frame: staged through the
+     * context's pinned slots, so they are free again when the call returns and the DMA runs at PCIe
+     * speed, ordered on the stream ahead of the kernels that read the image */
+    int rc = mltcuda_upload_staged(ctx, ci->data, image, cuda_format_bytes(format, width, height));
     if (!rc && alpha)
-        rc = mltcuda_upload(ctx, ci->alpha, alpha, (size_t) width * height);
-    /* the source buffers are pageable and owned by the frame: finish before they can go away */
-    if (!rc)
-        rc = mltcuda_ctx_sync(ctx);
+        rc = mltcuda_upload_staged(ctx, ci->alpha, alpha, (size_t) width * height);
     if (rc) {
         mlt_log_error(NULL, "[cuda] upload failed: %s\n", mltcuda_last_error());
         cuda_image_close(ci);
@@ -169,17 +169,18 @@ static cuda_image upload_host_image(mlt_frame frame, mltcuda_ctx *ctx, const uin
 }
 
 /* Replace the frame's private image by a host copy in ci->format (+ alpha plane). */
-static int download_to_frame(mlt_frame frame, cuda_image ci, uint8_t **image, mlt_image_format *format)
+int cuda_download_to_frame(mlt_frame frame, cuda_image ci, uint8_t **image, mlt_image_format *format)
 {
     size_t bytes = cuda_format_bytes(ci->format, ci->width, ci->height);
     size_t abytes = ci->alpha ? (size_t) ci->width * ci->height : 0;
-    uint8_t *host = mlt_pool_alloc(bytes);
-    uint8_t *ahost = abytes ? mlt_pool_alloc(abytes) : NULL;
+    /* pinned destination from the recycling pool: the DMA lands in the buffer the frame will own */
+    uint8_t *host = mltcuda_host_pool_alloc(bytes);
+    uint8_t *ahost = abytes ? mltcuda_host_pool_alloc(abytes) : NULL;
     if (!host || (abytes && !ahost)) {
         if (host)
-            mlt_pool_release(host);
+            mltcuda_host_pool_release(host);
         if (ahost)
-            mlt_pool_release(ahost);
+            mltcuda_host_pool_release(ahost);
         return 1;
     }
     int rc = mltcuda_download(ci->ctx, host, ci->data, bytes);
@@ -190,17 +191,17 @@ static int download_to_frame(mlt_frame frame, cuda_image ci, uint8_t **image, ml
     if (rc) {
         mlt_log_error(NULL, "[cuda] download failed: %s\n", mltcuda_last_error());
         if (host)
-            mlt_pool_release(host);
+            mltcuda_host_pool_release(host);
         if (ahost)
-            mlt_pool_release(ahost);
+            mltcuda_host_pool_release(ahost);
         return 1;
     }
     mlt_properties p = MLT_FRAME_PROPERTIES(frame);
     mlt_image_format f = ci->format;
     mlt_properties_set(p, CUDA_IMAGE_TAG, NULL);
     mlt_properties_set_int(p, "format", f);
-    mlt_frame_set_image(frame, host, (int) bytes, mlt_pool_release); /* closes the handle */
-    mlt_frame_set_alpha(frame, ahost, (int) abytes, ahost ? mlt_pool_release : NULL);
+    mlt_frame_set_image(frame, host, (int) bytes, (mlt_destructor) mltcuda_host_pool_release); /* closes the handle */
+    mlt_frame_set_alpha(frame, ahost, (int) abytes, ahost ? (mlt_destructor) mltcuda_host_pool_release : NULL);
     *image = host, *format = f;
     return 0;
 }
@@ -308,7 +309,7 @@ int cuda_convert_image(mlt_frame frame, uint8_t **image, mlt_image_format *forma
         *image = (uint8_t *) ci, *format = mlt_image_private;
         if (resident)
             return 0;
-        return download_to_frame(frame, ci, image, format);
+        return cuda_download_to_frame(frame, ci, image, format);
     }
 
     /* ours, and a host consumer is asking: convert on the device when the matrix has the cell,
@@ -323,7 +324,7 @@ int cuda_convert_image(mlt_frame frame, uint8_t **image, mlt_image_format *forma
         }
         ci = c2;
     }
-    if (download_to_frame(frame, ci, image, format))
+    if (cuda_download_to_frame(frame, ci, image, format))
         return 1;
     if (*format != output)
         return mlt_frame_next_convert_image(frame, image, format, output);

@@ -63,6 +63,10 @@ int cuda_frame_set_image(mlt_frame frame, cuda_image ci);
  * returned handle stays owned by the frame.  NULL on error. */
 cuda_image cuda_frame_get_image(mlt_frame frame, mlt_image_format format, int *width, int *height, int writable);
 
+/* Replace the frame's device image `ci` by a host copy (pinned, recycled) in ci->format, with its
+ * alpha plane; *image / *format are updated.  Closes the handle. */
+int cuda_download_to_frame(mlt_frame frame, cuda_image ci, uint8_t **image, mlt_image_format *format);
+
 /* Convert a device image to another format on the device (imageconvert matrix).  Returns a NEW
  * image (caller owns) or NULL if the cell does not exist / on error. */
 cuda_image cuda_image_convert(cuda_image src, mlt_image_format to);
@@ -75,6 +79,7 @@ int cuda_convert_image(mlt_frame frame, uint8_t **image, mlt_image_format *forma
 uint16_t *cuda_cached_map(mlt_properties owner, const char *key, mltcuda_ctx *ctx, const uint16_t *host, int w, int h);
 
 /* --- constructors (one file per service) ---------------------------------------------------- */
+mlt_producer cuda_producer_noise_init(mlt_profile, mlt_service_type, const char *, char *);
 mlt_transition cuda_transition_composite_init(mlt_profile, mlt_service_type, const char *, char *);
 mlt_transition cuda_transition_luma_init(mlt_profile, mlt_service_type, const char *, char *);
 mlt_transition cuda_transition_affine_init(mlt_profile, mlt_service_type, const char *, char *);

@@ -44,6 +44,13 @@ static void *create_filter(mlt_profile profile, mlt_service_type type, const cha
     return NULL;
 }
 
+static void *create_producer(mlt_profile profile, mlt_service_type type, const char *id, const void *arg)
+{
+    if (!strcmp(base_name(id), "noise"))
+        return cuda_producer_noise_init(profile, type, id, (char *) arg);
+    return NULL;
+}
+
 static int override_enabled(void)
 {
     const char *e = getenv("MLT_CUDA_OVERRIDE");
@@ -66,6 +73,38 @@ static void on_filter_request(mlt_properties owner, void *unused, mlt_event_data
         return;
     if (!strcmp(d->name, "imageconvert"))
         *(void **) d->service = create_filter(NULL, mlt_service_filter_type, d->name, d->input);
+}
+
+/* producers: MLT_CUDA_PRODUCERS=0 keeps the stock CPU producers while the
+ * transitions stay overridden */
+static int producers_enabled(void)
+{
+    const char *e = getenv("MLT_CUDA_PRODUCERS");
+    return override_enabled() && !(e && (!strcmp(e, "0") || !strcmp(e, "off") || !strcmp(e, "no")));
+}
+
+/* "producer-create-request" carries no profile and the factory does not stamp one on a producer a
+ * listener supplies (mlt_factory.c:337-358), so the override hooks "producer-create-done" instead:
+ * the repository has just built the `noise` producer -- ours if this module registered the name
+ * last, the stock one otherwise (load order is readdir order, mlt_repository.c:79) -- and a stock
+ * one is swapped for ours built on the same profile before the factory stamps the common
+ * properties on it. */
+static void on_producer_done(mlt_properties owner, void *unused, mlt_event_data ev)
+{
+    mlt_factory_event_data *d = mlt_event_data_to_object(ev);
+    if (!d || !d->name || !d->service || !*(void **) d->service || !producers_enabled())
+        return;
+    if (strcmp(d->name, "noise"))
+        return;
+    mlt_producer stock = *(mlt_producer *) d->service;
+    if (mlt_properties_get_int(MLT_PRODUCER_PROPERTIES(stock), "_cuda_producer"))
+        return;
+    mlt_producer ours = create_producer(mlt_service_profile(MLT_PRODUCER_SERVICE(stock)), mlt_service_producer_type, d->name,
+                                        d->input);
+    if (ours) {
+        mlt_producer_close(stock);
+        *(mlt_producer *) d->service = ours;
+    }
 }
 
 static mlt_properties metadata(mlt_service_type type, const char *id, void *data)
@@ -97,9 +136,16 @@ MLT_REPOSITORY
         MLT_REGISTER(mlt_service_filter_type, "imageconvert", create_filter);
         MLT_REGISTER_METADATA(mlt_service_filter_type, "imageconvert", metadata, yml[3]);
     }
+    MLT_REGISTER(mlt_service_producer_type, "cuda.noise", create_producer);
+    MLT_REGISTER_METADATA(mlt_service_producer_type, "cuda.noise", metadata, "producer_noise.yml");
+    if (producers_enabled()) {
+        MLT_REGISTER(mlt_service_producer_type, "noise", create_producer);
+        MLT_REGISTER_METADATA(mlt_service_producer_type, "noise", metadata, "producer_noise.yml");
+    }
     mlt_properties events = mlt_factory_event_object();
     if (events) {
         mlt_events_listen(events, NULL, "transition-create-request", (mlt_listener) on_transition_request);
         mlt_events_listen(events, NULL, "filter-create-request", (mlt_listener) on_filter_request);
+        mlt_events_listen(events, NULL, "producer-create-done", (mlt_listener) on_producer_done);
     }
 }

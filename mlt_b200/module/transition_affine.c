@@ -220,6 +220,12 @@ static int affine_get_image(mlt_frame a_frame, uint8_t **image, mlt_image_format
         }
         r.o = (r.o == DBL_MIN) ? 1.0 : MIN(r.o, 1.0);
     }
+    /* The reference keeps the service locked through the B fetch and the transform unless
+     * threads == 1 (:511-514, 724-727), because its transform occupies the shared slice pool.  The
+     * GPU transform does not, and holding the lock over B's upload serialised the worker threads
+     * (cfg4 through melt: 190 -> frames/s of one thread).  Unlock here, as the reference does for
+     * threads == 1: everything below is per-frame state or internally locked property reads. */
+    mlt_service_unlock(service);
     r.x *= scale_w, r.y *= scale_h, r.w *= scale_w, r.h *= scale_h;
     const double geometry_w = r.w, geometry_h = r.h;
     const int fill = mlt_properties_get_int(props, "fill");
@@ -272,7 +278,6 @@ static int affine_get_image(mlt_frame a_frame, uint8_t **image, mlt_image_format
     cuda_image b = cuda_frame_get_image(b_frame, work, &b_width, &b_height, 0);
     if (!b) {
         mlt_frame_set_image(b_frame, NULL, 0, NULL);
-        mlt_service_unlock(service);
         return 1;
     }
 
@@ -349,7 +354,6 @@ out:
     /* drop the (potentially large) B image: stream-ordered free, safe after the launch */
     mlt_frame_set_image(b_frame, NULL, 0, NULL);
     mlt_properties_set(b_props, CUDA_IMAGE_TAG, NULL);
-    mlt_service_unlock(service);
     return rc;
 }
 

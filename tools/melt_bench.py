@@ -32,12 +32,22 @@ def run(cuda, frames, threads, profile, base):
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("--frames", type=int, default=120)
+    ap.add_argument("--frames", type=int, default=2400)
     ap.add_argument("--threads", type=int, default=os.cpu_count() or 1)
     ap.add_argument("--profile", default="uhd_2160p_60")
     a = ap.parse_args()
     base = tempfile.mkdtemp()
+    # Two run lengths per arm: the difference removes process start-up (CUDA initialisation, one
+    # context + pinned staging per worker thread, first-use kernel loading: 1.5-3 s for the module,
+    # 0.1 s for the stock services) and gives the steady-state rate a long timeline sees.
+    short = max(8, a.frames // 12)
     for cuda in (False, True):
-        run(cuda, 8, a.threads, a.profile, base)
-        fps, dt = run(cuda, a.frames, a.threads, a.profile, base)
-        print(f"{'cuda module' if cuda else 'stock (CPU)'}: {fps:.2f} frames/s ({a.frames} frames, {dt:.2f} s, real_time=-{a.threads}, {a.profile})", flush=True)
+        n = a.frames if cuda else max(short * 2, a.frames // 8)  # the stock arm is ~20x slower: fewer frames
+        s0 = short if cuda else max(8, n // 6)
+        _, t1 = run(cuda, s0, a.threads, a.profile, base)
+        fps, t2 = run(cuda, n, a.threads, a.profile, base)
+        a_frames, short_n = n, s0
+        steady = (a_frames - short_n) / max(t2 - t1, 1e-9)
+        print(f"{'cuda module' if cuda else 'stock (CPU)'}: {fps:.2f} frames/s over the whole run ({a_frames} frames, {t2:.2f} s), "
+              f"steady state {steady:.1f} frames/s, start-up ~{t1 - short_n / steady:.2f} s "
+              f"(real_time=-{a.threads}, {a.profile})", flush=True)
