@@ -340,6 +340,7 @@ cuda_image cuda_frame_get_image(mlt_frame frame, mlt_image_format format, int *w
     mlt_image_format got = mlt_image_private; /* ask for residency explicitly (see cuda_convert_image) */
     mlt_frame_prepend_convert_image(frame, cuda_convert_image);
     mlt_properties_set_int(p, CUDA_REQUESTED, mlt_properties_get_int(p, CUDA_REQUESTED) + 1);
+    mlt_properties_set_int(p, CUDA_WORK_FORMAT, format);
     int err = mlt_frame_get_image(frame, &img, &got, width, height, writable);
     mlt_properties_set_int(p, CUDA_REQUESTED, mlt_properties_get_int(p, CUDA_REQUESTED) - 1);
     if (err || !img)

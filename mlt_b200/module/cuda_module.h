@@ -28,6 +28,7 @@
 #define CUDA_IMAGE_TAG "mlt_image_private"
 #define CUDA_IMAGE_TAG_VALUE "cuda"
 #define CUDA_REQUESTED "_cuda_requested"
+#define CUDA_WORK_FORMAT "_cuda_work_format" /* format the pulling service will work in (hint for device producers) */
 
 typedef struct cuda_image_s
 {
@@ -80,6 +81,8 @@ uint16_t *cuda_cached_map(mlt_properties owner, const char *key, mltcuda_ctx *ct
 
 /* --- constructors (one file per service) ---------------------------------------------------- */
 mlt_producer cuda_producer_noise_init(mlt_profile, mlt_service_type, const char *, char *);
+mlt_producer cuda_producer_colour_init(mlt_profile, mlt_service_type, const char *, char *);
+extern __thread int cuda_creating_stock_producer;
 mlt_transition cuda_transition_composite_init(mlt_profile, mlt_service_type, const char *, char *);
 mlt_transition cuda_transition_luma_init(mlt_profile, mlt_service_type, const char *, char *);
 mlt_transition cuda_transition_affine_init(mlt_profile, mlt_service_type, const char *, char *);

@@ -46,8 +46,11 @@ static void *create_filter(mlt_profile profile, mlt_service_type type, const cha
 
 static void *create_producer(mlt_profile profile, mlt_service_type type, const char *id, const void *arg)
 {
-    if (!strcmp(base_name(id), "noise"))
+    const char *n = base_name(id);
+    if (!strcmp(n, "noise"))
         return cuda_producer_noise_init(profile, type, id, (char *) arg);
+    if (!strcmp(n, "colour") || !strcmp(n, "color"))
+        return cuda_producer_colour_init(profile, type, id, (char *) arg);
     return NULL;
 }
 
@@ -94,7 +97,7 @@ static void on_producer_done(mlt_properties owner, void *unused, mlt_event_data 
     mlt_factory_event_data *d = mlt_event_data_to_object(ev);
     if (!d || !d->name || !d->service || !*(void **) d->service || !producers_enabled())
         return;
-    if (strcmp(d->name, "noise"))
+    if (cuda_creating_stock_producer || (strcmp(d->name, "noise") && strcmp(d->name, "colour") && strcmp(d->name, "color")))
         return;
     mlt_producer stock = *(mlt_producer *) d->service;
     if (mlt_properties_get_int(MLT_PRODUCER_PROPERTIES(stock), "_cuda_producer"))
@@ -136,11 +139,15 @@ MLT_REPOSITORY
         MLT_REGISTER(mlt_service_filter_type, "imageconvert", create_filter);
         MLT_REGISTER_METADATA(mlt_service_filter_type, "imageconvert", metadata, yml[3]);
     }
+    MLT_REGISTER(mlt_service_producer_type, "cuda.colour", create_producer);
+    MLT_REGISTER_METADATA(mlt_service_producer_type, "cuda.colour", metadata, "producer_colour.yml");
     MLT_REGISTER(mlt_service_producer_type, "cuda.noise", create_producer);
     MLT_REGISTER_METADATA(mlt_service_producer_type, "cuda.noise", metadata, "producer_noise.yml");
     if (producers_enabled()) {
         MLT_REGISTER(mlt_service_producer_type, "noise", create_producer);
         MLT_REGISTER_METADATA(mlt_service_producer_type, "noise", metadata, "producer_noise.yml");
+        /* `colour` / `color` are NOT re-registered: the wrapper instantiates the stock producer by
+         * name for everything off the fast path, and is swapped in by on_producer_done */
     }
     mlt_properties events = mlt_factory_event_object();
     if (events) {

@@ -78,6 +78,13 @@ EXACT = [
     ("cfg1d_alpha_b", "yuv422", [10],
      A + ["-track", "colour:0x3060c0a0", "out=249", "-transition", "composite", "a_track=0", "b_track=1",
           "geometry=10%/10%:50%x50%:70%"]),
+    # opaque colour B: the stock producer hands yuv422 WITHOUT an alpha plane (SSE2 case 1, not 3)
+    ("comp_opaque_colour", "yuv422", [10],
+     A + ["-track", "colour:0xc04020ff", "out=249", "-transition", "composite", "a_track=0", "b_track=1",
+          "geometry=10%/10%:50%x50%:70%"]),
+    ("colour_checkerboard_rgba_out", "rgba", [3],
+     ["colour:checkerboard", "out=249", "-track", "colour:0x3060c0a0", "out=249", "-transition", "composite", "a_track=0",
+      "b_track=1", "geometry=20%/20%:40%x40%:60%"]),
     ("comp_keyframed_odd", "yuv422", [0, 77, 249],
      A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1",
                     "geometry=0=3/5:641x355:30%; 249=-101/-33:1501x901:90%"]),
