@@ -29,7 +29,7 @@ struct CompK
     int cpr; // chunks per row upper bound
 };
 
-__global__ void __launch_bounds__(256) k_composite_rows(CompK K)
+__global__ void __launch_bounds__(256, 8) k_composite_rows(CompK K)
 {
     // grid = (chunks of a row, row, frame): no div/mod in the index math
     const int c = blockIdx.x * blockDim.x + threadIdx.x;

@@ -75,7 +75,7 @@ __device__ __forceinline__ void luma_row_info(const LumaK &K, int i, int &field,
 }
 
 // luma_composite_yuv422 (:327-473) and, with map == NULL, dissolve_yuv422 (:131-190)
-template <bool DISSOLVE> __global__ void __launch_bounds__(256) k_luma_yuv422(LumaK K)
+template <bool DISSOLVE> __global__ void __launch_bounds__(256, 8) k_luma_yuv422(LumaK K)
 {
     const int c = blockIdx.x * blockDim.x + threadIdx.x; // grid = (chunks of a row, row, frame)
     if (c >= K.cpr)
@@ -138,16 +138,16 @@ template <bool DISSOLVE> __global__ void __launch_bounds__(256) k_luma_yuv422(Lu
             uint32_t qy = dp & 0xff, qc = dp >> 8, py = sp & 0xff, pc = sp >> 8;
             if (DISSOLVE) {
                 if (translucent && K.alpha_over) { // composite_line_yuv_float :63-86
-                    float mix_a = (1.0f - K.weight) * (float) (ad ? ad[j] : 255) / 255.f;
-                    float mix_b = K.weight * (float) (as ? as[j] : 255) / 255.f;
+                    float mix_a = mc_fdiv_const<255>((1.0f - K.weight) * (float) (ad ? ad[j] : 255));
+                    float mix_b = mc_fdiv_const<255>(K.weight * (float) (as ? as[j] : 255));
                     if (ad) {
                         float mix2 = mix_b + mix_a;
-                        ad[j] = (uint8_t) mc_f2u(255 * mix2, 0xff);
+                        ad[j] = (uint8_t) mc_f2u_pos(255 * mix2, 0xff);
                         if (mix2 != 0.f)
-                            mix_b /= mix2;
+                            mix_b = mc_fdiv_fast_rn(mix_b, mix2);
                     }
-                    qy = mc_f2u(py * mix_b + qy * (1.f - mix_b), 0xff);
-                    qc = mc_f2u(pc * mix_b + qc * (1.f - mix_b), 0xff);
+                    qy = mc_f2u_pos(py * mix_b + qy * (1.f - mix_b), 0xff);
+                    qc = mc_f2u_pos(pc * mix_b + qc * (1.f - mix_b), 0xff);
                     res = qy | (qc << 8);
                 } else { // composite_line_yuv(..., mix, NULL, 0, 0) :178-186
                     uint32_t aak = ad ? ad[j] : 0;
@@ -156,25 +156,25 @@ template <bool DISSOLVE> __global__ void __launch_bounds__(256) k_luma_yuv422(Lu
                         ad[j] = (uint8_t) aak;
                 }
             } else if (translucent) { // :417-451
-                float weight = (float) __ldg(l + ((j * K.x_diff) >> 16)) / 65535.f;
+                float weight = mc_fdiv_const<65535>((float) __ldg(l + ((j * K.x_diff) >> 16)));
                 float value = mc_smoothstep_f(weight, K.softness + weight, fpos);
-                float mix_a = (1.0f - value) * (float) (ad ? ad[j] : 255) / 255.f;
-                float mix_b = value * (float) (as ? as[j] : 255) / 255.f;
+                float mix_a = mc_fdiv_const<255>((1.0f - value) * (float) (ad ? ad[j] : 255));
+                float mix_b = mc_fdiv_const<255>(value * (float) (as ? as[j] : 255));
                 uint8_t *at = (K.invert && as) ? as : (!K.invert && ad) ? ad : nullptr;
                 if (at) {
                     float mix2 = mix_b + mix_a;
                     if (K.alpha_over) {
-                        at[j] = (uint8_t) mc_f2u(255 * mix2, 0xff);
+                        at[j] = (uint8_t) mc_f2u_pos(255 * mix2, 0xff);
                         if (mix2 != 0.f)
-                            mix_b /= mix2;
+                            mix_b = mc_fdiv_fast_rn(mix_b, mix2);
                     } else {
                         float tt = (float) at[j] + 255 * mix_b;
                         tt = tt < 0.f ? 0.f : tt > 255.f ? 255.f : tt;
-                        at[j] = (uint8_t) mc_f2u(tt, 0xff);
+                        at[j] = (uint8_t) mc_f2u_pos(tt, 0xff);
                     }
                 }
-                qy = mc_f2u(py * mix_b + qy * (1.f - mix_b), 0xff);
-                qc = mc_f2u(pc * mix_b + qc * (1.f - mix_b), 0xff);
+                qy = mc_f2u_pos(py * mix_b + qy * (1.f - mix_b), 0xff);
+                qc = mc_f2u_pos(pc * mix_b + qc * (1.f - mix_b), 0xff);
                 res = qy | (qc << 8);
             } else { // :452-463
                 uint32_t weight = __ldg(l + ((j * K.x_diff) >> 16));
@@ -203,10 +203,11 @@ template <bool DISSOLVE> __global__ void __launch_bounds__(256) k_luma_yuv422(Lu
 
 // luma_composite_rgba32/_rgba64 (:475-723) and dissolve_slice_rgba32/_rgba64 (:192-265).
 // T = uint8_t: 4 px per thread; uint16_t: 2 px per thread (16 bytes of A either way).
-template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256, 6) k_luma_rgba(LumaK K)
+template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256, sizeof(T) == 1 ? 6 : 8) k_luma_rgba(LumaK K)
 {
     constexpr int PPT = sizeof(T) == 1 ? 4 : 2;
     const float maxv = PxTraits<T>::maxv;
+    constexpr int MAXI = sizeof(T) == 1 ? 255 : 65535;
     const uint32_t mask = PxTraits<T>::mask;
     const int w = K.width_src, h = K.height_src;
     const long long npx = (long long) w * h;
@@ -313,15 +314,15 @@ template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256, 6) k
     for (int k = 0; k < PPT; k++) {
         if (p0 + k < npx) {
             if (DISSOLVE) {
-                float mix_a = (1.0f - K.weight) * (float) qv[k][3] / maxv;
-                float mix_b = K.weight * (float) pv[k][3] / maxv;
+                float mix_a = mc_fdiv_const<MAXI>((1.0f - K.weight) * (float) qv[k][3]);
+                float mix_b = mc_fdiv_const<MAXI>(K.weight * (float) pv[k][3]);
                 float mix2 = mix_b + mix_a;
                 if (mix2 != 0.f)
-                    mix_b /= mix2;
+                    mix_b = mc_fdiv_fast_rn(mix_b, mix2);
 #pragma unroll
                 for (int c = 0; c < 3; c++)
-                    qv[k][c] = mc_f2u(pv[k][c] * mix_b + qv[k][c] * (1.f - mix_b), mask);
-                qv[k][3] = mc_f2u(maxv * mix2, mask);
+                    qv[k][c] = mc_f2u_pos(pv[k][c] * mix_b + qv[k][c] * (1.f - mix_b), mask);
+                qv[k][3] = mc_f2u_pos(maxv * mix2, mask);
             } else {
                 if (k == 0 || j == 0) { // row-dependent terms: once per thread unless the group wraps
                     luma_row_info(K, i, field, y_off, ordinal);
@@ -330,23 +331,23 @@ template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256, 6) k
                 }
                 uint32_t lw = __ldg(lrow + ((j * K.x_diff) >> 16));
                 if (translucent) {
-                    float weight = (float) lw / 65535.f;
+                    float weight = mc_fdiv_const<65535>((float) lw);
                     float value = mc_smoothstep_f(weight, K.softness + weight, fpos);
-                    float mix_a = (1.0f - value) * (float) qv[k][3] / maxv;
-                    float mix_b = value * (float) pv[k][3] / maxv;
+                    float mix_a = mc_fdiv_const<MAXI>((1.0f - value) * (float) qv[k][3]);
+                    float mix_b = mc_fdiv_const<MAXI>(value * (float) pv[k][3]);
                     float mix2 = mix_b + mix_a;
                     if (K.alpha_over) {
-                        qv[k][3] = mc_f2u(maxv * mix2, mask);
+                        qv[k][3] = mc_f2u_pos(maxv * mix2, mask);
                         if (mix2 != 0.f)
-                            mix_b /= mix2;
+                            mix_b = mc_fdiv_fast_rn(mix_b, mix2);
                     } else {
                         float tt = (float) qv[k][3] + maxv * mix_b;
                         tt = tt < 0.f ? 0.f : tt > maxv ? maxv : tt;
-                        qv[k][3] = mc_f2u(tt, mask);
+                        qv[k][3] = mc_f2u_pos(tt, mask);
                     }
 #pragma unroll
                     for (int c = 0; c < 3; c++)
-                        qv[k][c] = mc_f2u(pv[k][c] * mix_b + qv[k][c] * (1.f - mix_b), mask);
+                        qv[k][c] = mc_f2u_pos(pv[k][c] * mix_b + qv[k][c] * (1.f - mix_b), mask);
                 } else {
                     uint32_t value = (uint32_t) mc_smoothstep((int32_t) lw, (int32_t) (K.i_softness + lw),
                                                               (uint32_t) ((1 << 16) * fpos), K.soft_magic);
