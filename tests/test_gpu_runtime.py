@@ -1,0 +1,60 @@
+"""C-ABI runtime pieces the MLT module leans on: staged uploads from pageable memory, the pinned
+host pool, cross-context ordering (include/mltcuda.h)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from mlt_b200 import Context, abi
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("nbytes", [1, 4095, 4 << 20, (4 << 20) + 1, (9 << 20) + 3, 33 << 20])
+def test_upload_staged_roundtrip(ctx, nbytes):
+    """Any size, incl. 0 / 1 / 2+ full 4 MiB staging slots plus a tail, arrives intact; the source may
+    be overwritten as soon as the call returns (mlt_pool buffers are recycled immediately)."""
+    rng = np.random.default_rng(nbytes)
+    src = rng.integers(0, 256, nbytes, dtype=np.uint8)
+    keep = src.copy()
+    d = ctx.alloc(nbytes)
+    abi.check(ctx.lib.mltcuda_upload_staged(ctx.h, d.ptr, src.ctypes.data_as(C.c_void_p), nbytes))
+    src[:] = 0  # released / reused by the caller
+    assert np.array_equal(ctx.get(d, (nbytes,)), keep)
+
+
+def test_host_pool_recycles_exact_sizes(ctx):
+    lib = ctx.lib
+    a = lib.mltcuda_host_pool_alloc(1 << 20)
+    b = lib.mltcuda_host_pool_alloc(1 << 20)
+    assert a and b and a != b
+    lib.mltcuda_host_pool_release(a)
+    c = lib.mltcuda_host_pool_alloc(1 << 20)  # same size: the released buffer comes back
+    assert c == a
+    d = lib.mltcuda_host_pool_alloc(2 << 20)  # other size: a fresh one
+    assert d not in (a, b)
+    # a pooled buffer is pinned: a download into it is a plain async DMA
+    dev = ctx.put(np.arange(256, dtype=np.uint8))
+    abi.check(lib.mltcuda_download(ctx.h, c, dev.ptr, 256))
+    ctx.sync()
+    got = np.ctypeslib.as_array(C.cast(c, C.POINTER(C.c_uint8)), shape=(256,))
+    assert np.array_equal(got, np.arange(256, dtype=np.uint8))
+    for p in (b, c, d):
+        lib.mltcuda_host_pool_release(p)
+
+
+def test_wait_event_orders_two_contexts(ctx):
+    """Work on a second context queued behind an event of the first sees the first one's result."""
+    lib = ctx.lib
+    other = Context(lib.mltcuda_ctx_device(ctx.h))
+    n = 8 << 20
+    a, b = ctx.alloc(n), ctx.alloc(n)
+    ev = lib.mltcuda_event_create()
+    for value in (0x11, 0x77):
+        abi.check(lib.mltcuda_memset(ctx.h, a.ptr, value, n))
+        abi.check(lib.mltcuda_event_record(ctx.h, ev))
+        abi.check(lib.mltcuda_ctx_wait_event(other.h, ev))
+        abi.check(lib.mltcuda_copy(other.h, b.ptr, a.ptr, n))
+        other.sync()
+        assert int(ctx.get(b, (n,)).min()) == value and int(ctx.get(b, (n,)).max()) == value
+    lib.mltcuda_event_destroy(ev)
