@@ -76,6 +76,15 @@ __host__ __device__ constexpr int sig_len(uint32_t sig)
     return n;
 }
 
+// index of the first slot of SIG holding `code`, or -1
+__host__ __device__ constexpr int sig_first(uint32_t sig, uint32_t code)
+{
+    for (int i = 0; sig; i++, sig >>= 4)
+        if ((sig & 15) == code)
+            return i;
+    return -1;
+}
+
 template <bool ONLY_BL, uint32_t SIG>
 __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_constant__ TractorK K)
 {
@@ -107,6 +116,24 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
         uint4 v0 = ldg16(p), v1 = ldg16(p + 16);
         rgba[0] = v0.x, rgba[1] = v0.y, rgba[2] = v0.z, rgba[3] = v0.w;
         rgba[4] = v1.x, rgba[5] = v1.y, rgba[6] = v1.z, rgba[7] = v1.w;
+    }
+
+    // The first affine op's warp-level classification (row terms + the mapped ends of the warp's
+    // 256-pixel span, all fp64 and independent of pixel data) is computed here, right behind the A
+    // load, so it runs under that load's latency instead of after the first use of A.
+    constexpr int AFF0 = sig_first(SIG, 2);
+    AffineRow preR = {0.0, 0.0};
+    double pre_xw0 = 0.0;
+    bool pre_rej = false, pre_all = false;
+    if (ONLY_BL && AFF0 >= 0 && fullwarp) {
+        const AffineParams &P = K.ops[AFF0 < 0 ? 0 : AFF0].a.ap;
+        preR = mc_affine_row(P, r);
+        pre_xw0 = P.lower_x + (double) (blockIdx.x * 256);
+        double ax, ay, bx, by;
+        mc_affine_map_x(P, preR, pre_xw0, ax, ay);
+        mc_affine_map_x(P, preR, pre_xw0 + 255.0, bx, by);
+        pre_rej = mc_affine_reject2(P, ax, ay, bx, by);
+        pre_all = mc_affine_inside(P, ax, ay) && mc_affine_inside(P, bx, by);
     }
 
     const int n_ops = SIG ? sig_len(SIG) : K.n_ops;
@@ -156,7 +183,8 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
             }
         } else if (code == 2) {
             const AffineParams &P = op.a.ap;
-            const AffineRow R = mc_affine_row(P, r);
+            const bool pre = ONLY_BL && AFF0 >= 0 && oi == AFF0;
+            const AffineRow R = pre ? preR : mc_affine_row(P, r);
             if (ONLY_BL && fullwarp) {
                 // Transposed pass.  With 8 consecutive pixels per thread the 32 lanes of a tap load
                 // are 8 destination pixels apart -- up to 32 different L1 lines per LDG, which made the
@@ -165,13 +193,20 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
                 // one tap load then touches 2-4 adjacent lines.  Same per-pixel arithmetic as below.
                 __syncwarp();
                 const int wcol0 = blockIdx.x * 256;
-                const double xw0 = P.lower_x + (double) wcol0;
-                double ax, ay, bx, by;
-                mc_affine_map_x(P, R, xw0, ax, ay);
-                mc_affine_map_x(P, R, xw0 + 255.0, bx, by);
-                if (mc_affine_reject2(P, ax, ay, bx, by))
+                double xw0;
+                bool rej, all;
+                if (pre) {
+                    xw0 = pre_xw0, rej = pre_rej, all = pre_all;
+                } else {
+                    xw0 = P.lower_x + (double) wcol0;
+                    double ax, ay, bx, by;
+                    mc_affine_map_x(P, R, xw0, ax, ay);
+                    mc_affine_map_x(P, R, xw0 + 255.0, bx, by);
+                    rej = mc_affine_reject2(P, ax, ay, bx, by);
+                    all = mc_affine_inside(P, ax, ay) && mc_affine_inside(P, bx, by);
+                }
+                if (rej)
                     continue; // warp-uniform
-                const bool all = mc_affine_inside(P, ax, ay) && mc_affine_inside(P, bx, by);
                 const uint8_t *bimg = op.a.b_image + b * op.a.b_bs;
                 asm volatile("" : "+l"(bimg));
                 uint32_t *sm = s_xpose[threadIdx.y];
