@@ -203,7 +203,10 @@ template <bool DISSOLVE> __global__ void __launch_bounds__(256, 8) k_luma_yuv422
 
 // luma_composite_rgba32/_rgba64 (:475-723) and dissolve_slice_rgba32/_rgba64 (:192-265).
 // T = uint8_t: 4 px per thread; uint16_t: 2 px per thread (16 bytes of A either way).
-template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256, sizeof(T) == 1 ? 6 : 8) k_luma_rgba(LumaK K)
+// WHOLE (row width a multiple of the group): every group is full and inside one row, so only the
+// straight-line whole-group paths are instantiated (fewer registers: 8 CTAs/SM).
+template <typename T, bool DISSOLVE, bool WHOLE>
+__global__ void __launch_bounds__(256, (WHOLE || sizeof(T) == 2) ? 8 : 6) k_luma_rgba(LumaK K)
 {
     constexpr int PPT = sizeof(T) == 1 ? 4 : 2;
     const float maxv = PxTraits<T>::maxv;
@@ -216,7 +219,7 @@ template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256, size
     // Otherwise grid = (groups of a frame, 1, frame); a frame has < 2^31 pixels: 32-bit index math.
     unsigned gid;
     int i, j;
-    if (K.cpr > 0) {
+    if (WHOLE || K.cpr > 0) {
         const int g = blockIdx.x * 32 + threadIdx.x;
         i = blockIdx.y * 8 + threadIdx.y;
         if (g >= K.cpr || i >= h)
@@ -235,8 +238,9 @@ template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256, size
     T *q = reinterpret_cast<T *>(K.dest + b * K.dest_bs) + (size_t) p0 * 4;
     const T *p = reinterpret_cast<const T *>(K.src + b * K.src_bs) + (size_t) p0 * 4;
     uint32_t qv[PPT][4], pv[PPT][4];
-    const bool full = p0 + PPT <= npx;
-    if (full) {
+    const bool full = WHOLE || p0 + PPT <= npx;
+    if (WHOLE) {
+    } else if (full) {
         uint4 a = ld16(q), s = ldg16(p);
         uint32_t aw[4] = {a.x, a.y, a.z, a.w}, sw[4] = {s.x, s.y, s.z, s.w};
 #pragma unroll
@@ -261,7 +265,7 @@ template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256, size
     int field = 0, y_off = 0, ordinal = 0;
     const uint16_t *lrow = nullptr;
     float fpos = 0.f;
-    if (!DISSOLVE && !translucent && full && j + PPT <= w) {
+    if (!DISSOLVE && !translucent && full && (WHOLE || j + PPT <= w)) {
         // opaque wipe, whole group inside one row (:576-590, :693-707): RGB mixed in integers, alpha kept
         luma_row_info(K, i, field, y_off, ordinal);
         fpos = field ? K.field_pos1 : K.field_pos0;
@@ -305,6 +309,61 @@ template <typename T, bool DISSOLVE> __global__ void __launch_bounds__(256, size
                     aw[2 * k] = __byte_perm(c0, c1, 0x7632);
                     aw[2 * k + 1] = __byte_perm(c2, aw[2 * k + 1], 0x7632);
                 }
+            }
+        }
+        *reinterpret_cast<uint4 *>(q) = make_uint4(aw[0], aw[1], aw[2], aw[3]);
+        return;
+    }
+    if (WHOLE || (full && (DISSOLVE || (translucent && j + PPT <= w)))) {
+        // translucent wipe / dissolve, whole group (:192-265, :592-640, :709-757): the float formula of
+        // the loop below, straight-line, with byte -> float by PRMT and truncation off the XU pipe
+        const float2 unbias = make_float2(-8388608.0f, -8388608.0f);
+        if (!DISSOLVE) {
+            luma_row_info(K, i, field, y_off, ordinal);
+            fpos = field ? K.field_pos1 : K.field_pos0;
+            lrow = K.map + (long) (y_off >> 16) * (K.luma_width * K.field_count);
+        }
+        uint4 a = ld16(q), s = ldg16(p);
+        uint32_t aw[4] = {a.x, a.y, a.z, a.w}, sw[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+            PxB<T> P, Q;
+            if constexpr (sizeof(T) == 1) {
+                P.from_word(sw[k]), Q.from_word(aw[k]);
+            } else {
+                P.from_word(make_uint2(sw[2 * k], sw[2 * k + 1])), Q.from_word(make_uint2(aw[2 * k], aw[2 * k + 1]));
+            }
+            const float2 p_lo = f2_add(P.lo, unbias), p_hi = f2_add(P.hi, unbias);
+            const float2 q_lo = f2_add(Q.lo, unbias), q_hi = f2_add(Q.hi, unbias);
+            float value = K.weight;
+            if (!DISSOLVE) {
+                const uint32_t lw = __ldg(lrow + (((uint32_t) (j + k) * (uint32_t) K.x_diff) >> 16));
+                const float weight = mc_fdiv_const<65535>((float) lw);
+                value = mc_smoothstep_f(weight, K.softness + weight, fpos);
+            }
+            const float mix_a = mc_fdiv_const<MAXI>((1.0f - value) * q_hi.y);
+            float mix_b = mc_fdiv_const<MAXI>(value * p_hi.y);
+            const float mix2 = mix_b + mix_a;
+            uint32_t o3;
+            if (DISSOLVE || K.alpha_over) {
+                o3 = mc_trunc_bits(maxv * mix2);
+                if (mix2 != 0.f)
+                    mix_b = mc_fdiv_fast_rn(mix_b, mix2);
+            } else {
+                float tt = q_hi.y + maxv * mix_b;
+                tt = tt < 0.f ? 0.f : tt > maxv ? maxv : tt;
+                o3 = mc_trunc_bits(tt);
+            }
+            const float imix = 1.f - mix_b;
+            // p * mix_b + q * (1 - mix_b): both products rounded, then the sum
+            const float2 t_lo = f2_mul(p_lo, f2_dup(mix_b));
+            const float2 o_lo = f2_lerp(t_lo, q_lo, imix);
+            const float o_b = p_hi.x * mix_b + q_hi.x * imix;
+            if constexpr (sizeof(T) == 1) {
+                aw[k] = PxB<T>::pack(mc_trunc_bits(o_lo.x), mc_trunc_bits(o_lo.y), mc_trunc_bits(o_b), o3);
+            } else {
+                const uint2 o = PxB<T>::pack(mc_trunc_bits(o_lo.x), mc_trunc_bits(o_lo.y), mc_trunc_bits(o_b), o3);
+                aw[2 * k] = o.x, aw[2 * k + 1] = o.y;
             }
         }
         *reinterpret_cast<uint4 *>(q) = make_uint4(aw[0], aw[1], aw[2], aw[3]);
@@ -515,16 +574,16 @@ extern "C" int mltcuda_luma(mltcuda_ctx *ctx, const mltcuda_luma_desc *d)
             K.cpr = K.width_src / ppt;
             blocks = dim3((K.cpr + 31) / 32, (K.height_src + 7) / 8, K.batch), threads = dim3(32, 8, 1);
         }
-        if (fmt == MLTCUDA_FMT_RGBA) {
-            if (dissolve)
-                k_luma_rgba<uint8_t, true><<<blocks, threads, 0, ctx->stream>>>(K);
-            else
-                k_luma_rgba<uint8_t, false><<<blocks, threads, 0, ctx->stream>>>(K);
-        } else {
-            if (dissolve)
-                k_luma_rgba<uint16_t, true><<<blocks, threads, 0, ctx->stream>>>(K);
-            else
-                k_luma_rgba<uint16_t, false><<<blocks, threads, 0, ctx->stream>>>(K);
+        const int sel = (fmt == MLTCUDA_FMT_RGBA ? 0 : 4) | (dissolve ? 2 : 0) | (K.cpr > 0 ? 1 : 0);
+        switch (sel) {
+        case 0: k_luma_rgba<uint8_t, false, false><<<blocks, threads, 0, ctx->stream>>>(K); break;
+        case 1: k_luma_rgba<uint8_t, false, true><<<blocks, threads, 0, ctx->stream>>>(K); break;
+        case 2: k_luma_rgba<uint8_t, true, false><<<blocks, threads, 0, ctx->stream>>>(K); break;
+        case 3: k_luma_rgba<uint8_t, true, true><<<blocks, threads, 0, ctx->stream>>>(K); break;
+        case 4: k_luma_rgba<uint16_t, false, false><<<blocks, threads, 0, ctx->stream>>>(K); break;
+        case 5: k_luma_rgba<uint16_t, false, true><<<blocks, threads, 0, ctx->stream>>>(K); break;
+        case 6: k_luma_rgba<uint16_t, true, false><<<blocks, threads, 0, ctx->stream>>>(K); break;
+        default: k_luma_rgba<uint16_t, true, true><<<blocks, threads, 0, ctx->stream>>>(K); break;
         }
         rc = mc_after_launch(ctx, "k_luma_rgba");
     }
