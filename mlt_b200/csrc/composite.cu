@@ -45,7 +45,11 @@ __global__ void __launch_bounds__(256, 8) k_composite_rows(CompK K)
         return;
     int jlo = j0 < 0 ? 0 : j0, jhi = j0 + 8 > P.width ? P.width : j0 + 8; // valid [jlo, jhi)
     uint4 *dptr = reinterpret_cast<uint4 *>(drow + 2 * (long) j0);        // 16-byte aligned
-    uint4 dv = ld16(dptr);
+    // a whole group of a blit (SSE2 cases 0/4: memcpy + memset) overwrites A: do not read it
+    const bool overwrite = P.blit && jlo == j0 && jhi == j0 + 8;
+    uint4 dv = make_uint4(0, 0, 0, 0);
+    if (!overwrite)
+        dv = ld16(dptr);
     uint32_t d[4] = {dv.x, dv.y, dv.z, dv.w};
 
     uintptr_t srow = (uintptr_t) (K.src + b * K.src_bs + r * K.stride_src);
@@ -62,7 +66,8 @@ __global__ void __launch_bounds__(256, 8) k_composite_rows(CompK K)
         aarow = K.alpha_a + b * K.aa_bs + r * K.stride_aa;
         // read-modify-write: coherent byte/vector loads (no __ldg)
         uintptr_t a = (uintptr_t) aarow + j0;
-        if ((a & 7) == 0 && jlo == j0 && jhi == j0 + 8) {
+        if (overwrite) {
+        } else if ((a & 7) == 0 && jlo == j0 && jhi == j0 + 8) {
             uint2 v = ld8((const void *) a);
             aa[0] = v.x, aa[1] = v.y;
         } else {

@@ -8,8 +8,8 @@
 // (and the buffer is filled from its END backwards).  A lag-1 MWC with multiplier a and base 2^16
 // satisfies t[n+1] = a*t[n] mod (a*2^16-1) once the state is below the modulus (true from the 2nd
 // step on), so the state at step n is a^(n-2)*t[2] mod m: each thread jumps straight to the state
-// of the last pixel of its 8-pixel group with three table look-ups (a^n split into 12+12+8 bit
-// digits) and then steps the generators 8 times exactly like the reference.  Bit-exact.
+// of the last pixel of its 64-pixel group with three table look-ups (a^n split into 12+12+8 bit
+// digits) and then steps the generator 64 times exactly like the reference.  Bit-exact.
 #include "common.cuh"
 #include "pixel_ops.cuh"
 
@@ -39,12 +39,14 @@ __device__ __forceinline__ uint32_t mwc_pow(const uint32_t *tab, uint64_t mod, u
 
 // The pixel byte is ((x << 16) + (y & 65535)) & 0xff == y & 0xff (producer_noise.c:118): the x
 // generator never reaches the image, so only the y generator (multiplier 30903) is evaluated.
-// One thread = 16 pixels (two 16-byte stores); grid = (groups of a frame, 1, frame).
-constexpr int NOISE_PPT = 16;
-__global__ void __launch_bounds__(256) k_noise(uint8_t *dst, unsigned npx, uint32_t y2, uint32_t y0,
+// One thread = 64 pixels (eight 16-byte stores); grid = (groups of a frame, 1, frame).
+constexpr int NOISE_PPT = 64, NOISE_THREADS = 128; // PPT / 8 must be a power of two <= 8
+__global__ void __launch_bounds__(NOISE_THREADS) k_noise(uint8_t *dst, unsigned npx, uint32_t y2, uint32_t y0,
                                                const uint32_t *tab, size_t bs, int position, uint64_t M)
 {
     const unsigned c = blockIdx.x * blockDim.x + threadIdx.x;
+    // every lane of the warp owns a whole group: stores go through shared memory (below)
+    const bool fullwarp = __ballot_sync(0xffffffffu, ((unsigned long long) c + 1) * NOISE_PPT <= npx) == 0xffffffffu;
     if ((unsigned long long) c * NOISE_PPT >= npx)
         return;
     const int b = blockIdx.z;
@@ -65,10 +67,49 @@ __global__ void __launch_bounds__(256) k_noise(uint8_t *dst, unsigned npx, uint3
     else
         y = MWC_B * (y0 & 65535) + (y0 >> 16);
     uint32_t w[NOISE_PPT / 2];
+    const int cnt = (int) (hi - lo) + 1;
+    uint8_t *d = dst + b * bs + (size_t) lo * 2;
+    if (cnt == NOISE_PPT) { // whole group: no per-pixel predicates
+#pragma unroll
+        for (int k = NOISE_PPT / 2 - 1; k >= 0; k--) {
+            // clamp(v, 16, 240) - 16 = relu(min(v - 16, 224)), one VIADDMNMX.RELU; the + 16 and
+            // U/V = 128 are added per pair
+            int v0, v1;
+            asm("min.relu.s32 %0, %1, 224;" : "=r"(v1) : "r"((int) (y & 0xff) - 16));
+            y = MWC_B * (y & 65535) + (y >> 16);
+            asm("min.relu.s32 %0, %1, 224;" : "=r"(v0) : "r"((int) (y & 0xff) - 16));
+            y = MWC_B * (y & 65535) + (y >> 16);
+            w[k] = __byte_perm(v0, v1, 0x1410) + 0x80108010u; // byte 1 of v0 is zero
+        }
+        constexpr int U = NOISE_PPT / 8; // 16-byte units per thread
+        if (fullwarp) {
+            // A thread's 128 bytes are contiguous, so a direct 16-byte store instruction would touch
+            // 32 separate 128-byte-strided pieces.  Transpose through shared memory (16-byte units,
+            // XOR-swizzled: conflict-free both ways) so each store instruction writes 512
+            // contiguous bytes of the warp's 4 KiB.
+            __shared__ uint4 s_t[NOISE_THREADS / 32][32 * U];
+            uint4 *sm = s_t[threadIdx.x >> 5];
+            const int l = threadIdx.x & 31;
+#pragma unroll
+            for (int k = 0; k < U; k++)
+                sm[U * l + (k ^ (l & (U - 1)))] = make_uint4(w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
+            __syncwarp();
+            uint4 *dw = reinterpret_cast<uint4 *>(d - (size_t) l * (NOISE_PPT * 2)); // the warp's first byte
+#pragma unroll
+            for (int k = 0; k < U; k++) {
+                const int i = 32 * k + l, lp = i / U;
+                dw[i] = sm[U * lp + ((i & (U - 1)) ^ (lp & (U - 1)))];
+            }
+            return;
+        }
+#pragma unroll
+        for (int k = 0; k < U; k++)
+            reinterpret_cast<uint4 *>(d)[k] = make_uint4(w[4 * k], w[4 * k + 1], w[4 * k + 2], w[4 * k + 3]);
+        return;
+    }
 #pragma unroll
     for (int k = 0; k < NOISE_PPT / 2; k++)
         w[k] = 0;
-    const int cnt = (int) (hi - lo) + 1;
 #pragma unroll
     for (int k = NOISE_PPT - 1; k >= 0; k--) {
         if (k < cnt) {
@@ -78,16 +119,10 @@ __global__ void __launch_bounds__(256) k_noise(uint8_t *dst, unsigned npx, uint3
             y = MWC_B * (y & 65535) + (y >> 16);
         }
     }
-    uint8_t *d = dst + b * bs + (size_t) lo * 2;
-    if (cnt == NOISE_PPT) {
-        reinterpret_cast<uint4 *>(d)[0] = make_uint4(w[0], w[1], w[2], w[3]);
-        reinterpret_cast<uint4 *>(d)[1] = make_uint4(w[4], w[5], w[6], w[7]);
-    } else {
 #pragma unroll
-        for (int k = 0; k < NOISE_PPT; k++)
-            if (k < cnt)
-                reinterpret_cast<uint16_t *>(d)[k] = (uint16_t) (w[k >> 1] >> ((k & 1) * 16));
-    }
+    for (int k = 0; k < NOISE_PPT; k++)
+        if (k < cnt)
+            reinterpret_cast<uint16_t *>(d)[k] = (uint16_t) (w[k >> 1] >> ((k & 1) * 16));
 }
 
 __global__ void __launch_bounds__(256) k_fill16(uint4 *dst, size_t n16, uint4 v)
@@ -186,8 +221,8 @@ extern "C" int mltcuda_noise(mltcuda_ctx *ctx, uint8_t *dst, int width, int heig
         x = MWC_A * (x & 65535) + (x >> 16), y = MWC_B * (y & 65535) + (y >> 16);
     MC_BADARG(npx >= (1ll << 31) || batch > 65535, "frame too large / too many frames for one launch");
     (void) x, (void) x0;
-    dim3 grd(mc_blocks((npx + NOISE_PPT - 1) / NOISE_PPT, 256), 1, batch);
-    k_noise<<<grd, 256, 0, ctx->stream>>>(dst, (unsigned) npx, y, y0, ctx->noise_tab, dst_bstride, position, ~0ull / MOD_B);
+    dim3 grd(mc_blocks((npx + NOISE_PPT - 1) / NOISE_PPT, NOISE_THREADS), 1, batch);
+    k_noise<<<grd, NOISE_THREADS, 0, ctx->stream>>>(dst, (unsigned) npx, y, y0, ctx->noise_tab, dst_bstride, position, ~0ull / MOD_B);
     return mc_after_launch(ctx, "k_noise");
 }
 
