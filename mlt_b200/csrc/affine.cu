@@ -121,6 +121,8 @@ template <typename T, int INTERP> __global__ void __launch_bounds__(256) k_affin
         return;
     const int b = blockIdx.z;
     const AffineParams &P = K.p;
+    if (mc_affine_bb_reject(P, i, j, PPT))
+        return;
     const AffineRow R = mc_affine_row(P, i);
     double dxs[PPT], dys[PPT];
     // x of pixel j + k = (lower_x + j) + k: the reference steps x by ++ from lower_x (:361-363), so both
@@ -211,6 +213,27 @@ int mc_fill_affine_params(AffineParams &p, const mltcuda_affine_desc *d)
     // ... except bilinear on a 1-wide / 1-high B, which the reference does produce (App. B-3) and
     // whose result is well defined (mc_interp_bl): served by the generic kernel with clamped taps.
     p.degenerate = d->interp == MLTCUDA_INTERP_BL && d->b_width >= 1 && d->b_height >= 1 && (d->b_width < 2 || d->b_height < 2);
+    // bounding box of the accepted destination pixels: the four corners of [minima, xmax] x [minima, ymax]
+    // mapped back through dx = (m00 x + m01 y + m02) rdz + x_offset, dy likewise
+    p.bb_j0 = p.bb_i0 = INT_MIN / 2, p.bb_j1 = p.bb_i1 = INT_MAX / 2;
+    const double det = p.m00 * p.m11 - p.m01 * p.m10;
+    if (std::isfinite(det) && std::fabs(det) > 1e-12 && std::isfinite(p.rdz) && p.rdz != 0.0) {
+        double lo_x = INFINITY, hi_x = -INFINITY, lo_y = INFINITY, hi_y = -INFINITY;
+        for (int c = 0; c < 4; c++) {
+            const double u = (((c & 1) ? p.xmax : p.minima) - p.x_offset) / p.rdz - p.m02;
+            const double v = (((c & 2) ? p.ymax : p.minima) - p.y_offset) / p.rdz - p.m12;
+            const double x = (p.m11 * u - p.m01 * v) / det, y = (p.m00 * v - p.m10 * u) / det;
+            lo_x = std::fmin(lo_x, x), hi_x = std::fmax(hi_x, x), lo_y = std::fmin(lo_y, y), hi_y = std::fmax(hi_y, y);
+        }
+        lo_x -= p.lower_x, hi_x -= p.lower_x, lo_y -= p.lower_y, hi_y -= p.lower_y;
+        if (std::isfinite(lo_x) && std::isfinite(hi_x) && std::isfinite(lo_y) && std::isfinite(hi_y)
+            && std::fabs(lo_x) < 1e9 && std::fabs(hi_x) < 1e9 && std::fabs(lo_y) < 1e9 && std::fabs(hi_y) < 1e9) {
+            // margin: 2 px + a relative part for the rounding of the inverse on large coordinates
+            const double mx = 2.0 + 1e-9 * (std::fabs(lo_x) + std::fabs(hi_x)), my = 2.0 + 1e-9 * (std::fabs(lo_y) + std::fabs(hi_y));
+            p.bb_j0 = (int) std::floor(lo_x - mx), p.bb_j1 = (int) std::ceil(hi_x + mx);
+            p.bb_i0 = (int) std::floor(lo_y - my), p.bb_i1 = (int) std::ceil(hi_y + my);
+        }
+    }
     int need = d->interp == MLTCUDA_INTERP_BL ? 2 : d->interp == MLTCUDA_INTERP_BC ? 4 : 1;
     if (!p.degenerate && (d->b_width < need || d->b_height < need)) {
         mltcuda_set_error("affine: B image %dx%d smaller than the %dx%d sampler footprint", d->b_width, d->b_height, need, need);

@@ -127,13 +127,16 @@ __global__ void __launch_bounds__(256, ONLY_BL ? 4 : 1) k_tractor(const __grid_c
     bool pre_rej = false, pre_all = false;
     if (ONLY_BL && AFF0 >= 0 && fullwarp) {
         const AffineParams &P = K.ops[AFF0 < 0 ? 0 : AFF0].a.ap;
-        preR = mc_affine_row(P, r);
-        pre_xw0 = P.lower_x + (double) (blockIdx.x * 256);
-        double ax, ay, bx, by;
-        mc_affine_map_x(P, preR, pre_xw0, ax, ay);
-        mc_affine_map_x(P, preR, pre_xw0 + 255.0, bx, by);
-        pre_rej = mc_affine_reject2(P, ax, ay, bx, by);
-        pre_all = mc_affine_inside(P, ax, ay) && mc_affine_inside(P, bx, by);
+        pre_rej = mc_affine_bb_reject(P, r, blockIdx.x * 256, 256); // warp-uniform integer pre-test
+        if (!pre_rej) {
+            preR = mc_affine_row(P, r);
+            pre_xw0 = P.lower_x + (double) (blockIdx.x * 256);
+            double ax, ay, bx, by;
+            mc_affine_map_x(P, preR, pre_xw0, ax, ay);
+            mc_affine_map_x(P, preR, pre_xw0 + 255.0, bx, by);
+            pre_rej = mc_affine_reject2(P, ax, ay, bx, by);
+            pre_all = mc_affine_inside(P, ax, ay) && mc_affine_inside(P, bx, by);
+        }
     }
 
     const int n_ops = SIG ? sig_len(SIG) : K.n_ops;
