@@ -42,6 +42,50 @@ mltcuda_ctx *cuda_thread_ctx(void)
     return c;
 }
 
+/* ---- MLT_CUDA_STATS ---------------------------------------------------------------------------- */
+
+#include <stdatomic.h>
+#include <time.h>
+int cuda_stats_on = 0;
+static _Atomic uint64_t g_stat_ns[CS_N], g_stat_calls[CS_N];
+static const char *g_stat_name[CS_N] = {"composite get_image (incl. inputs)", "luma get_image (incl. inputs)", "affine get_image (incl. inputs)",
+                                        "convert_image (incl. download)", "noise producer", "colour producer", "download + sync",
+                                        "upload", "cuda_frame_get_image (pull input)", "-", "ctx sync"};
+uint64_t cuda_stat_now(void)
+{
+    struct timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return (uint64_t) ts.tv_sec * 1000000000ull + (uint64_t) ts.tv_nsec;
+}
+void cuda_stat_add(int id, uint64_t t0)
+{
+    atomic_fetch_add(&g_stat_ns[id], cuda_stat_now() - t0);
+    atomic_fetch_add(&g_stat_calls[id], 1);
+}
+static void cuda_stats_print(void)
+{
+    for (int i = 0; i < CS_N; i++)
+        if (g_stat_calls[i])
+            fprintf(stderr, "[cuda stats] %-36s calls %8llu  total %9.1f ms  mean %8.1f us\n", g_stat_name[i],
+                    (unsigned long long) g_stat_calls[i], g_stat_ns[i] / 1e6, g_stat_ns[i] / 1e3 / g_stat_calls[i]);
+}
+__attribute__((constructor)) static void cuda_stats_init(void)
+{
+    const char *e = getenv("MLT_CUDA_STATS");
+    if (e && *e && *e != '0') {
+        cuda_stats_on = 1;
+        atexit(cuda_stats_print);
+    }
+}
+
+int cuda_request_resident(mlt_frame frame, mlt_image_format requested)
+{
+    mlt_properties p = MLT_FRAME_PROPERTIES(frame);
+    if (mlt_properties_get_int(p, CUDA_REQUESTED) <= 0)
+        return 0;
+    return requested == mlt_image_private || mlt_properties_get_int(p, CUDA_PASSTHROUGH) > 0;
+}
+
 /* ---- formats ---------------------------------------------------------------------------------- */
 
 int cuda_format_supported(mlt_image_format f)
@@ -145,7 +189,7 @@ int cuda_frame_set_image(mlt_frame frame, cuda_image ci)
 
 /* ---- host <-> device ---------------------------------------------------------------------------- */
 
-static cuda_image upload_host_image(mlt_frame frame, mltcuda_ctx *ctx, const uint8_t *image, mlt_image_format format,
+static cuda_image upload_host_image_impl(mlt_frame frame, mltcuda_ctx *ctx, const uint8_t *image, mlt_image_format format,
                                     int width, int height)
 {
     const uint8_t *alpha = NULL;
@@ -168,11 +212,21 @@ static cuda_image upload_host_image(mlt_frame frame, mltcuda_ctx *ctx, const uin
     return ci;
 }
 
+static cuda_image upload_host_image(mlt_frame frame, mltcuda_ctx *ctx, const uint8_t *image, mlt_image_format format, int width,
+                                    int height)
+{
+    const uint64_t st0 = CUDA_STAT_T0();
+    cuda_image ci = upload_host_image_impl(frame, ctx, image, format, width, height);
+    CUDA_STAT_END(CS_UPLOAD, st0);
+    return ci;
+}
+
 /* Replace the frame's private image by a host copy in ci->format (+ alpha plane). */
 int cuda_download_to_frame(mlt_frame frame, cuda_image ci, uint8_t **image, mlt_image_format *format)
 {
     size_t bytes = cuda_format_bytes(ci->format, ci->width, ci->height);
     size_t abytes = ci->alpha ? (size_t) ci->width * ci->height : 0;
+    const uint64_t st0 = CUDA_STAT_T0();
     /* pinned destination from the recycling pool: the DMA lands in the buffer the frame will own */
     uint8_t *host = mltcuda_host_pool_alloc(bytes);
     uint8_t *ahost = abytes ? mltcuda_host_pool_alloc(abytes) : NULL;
@@ -188,6 +242,7 @@ int cuda_download_to_frame(mlt_frame frame, cuda_image ci, uint8_t **image, mlt_
         rc = mltcuda_download(ci->ctx, ahost, ci->alpha, abytes);
     if (!rc)
         rc = mltcuda_ctx_sync(ci->ctx);
+    CUDA_STAT_END(CS_DOWNLOAD, st0);
     if (rc) {
         mlt_log_error(NULL, "[cuda] download failed: %s\n", mltcuda_last_error());
         if (host)
@@ -259,7 +314,7 @@ cuda_image cuda_image_convert(cuda_image src, mlt_image_format to)
 
 /* ---- the converter ---------------------------------------------------------------------------------- */
 
-int cuda_convert_image(mlt_frame frame, uint8_t **image, mlt_image_format *format, mlt_image_format output)
+static int cuda_convert_image_impl(mlt_frame frame, uint8_t **image, mlt_image_format *format, mlt_image_format output)
 {
     if (!image || !*image)
         return 1;
@@ -278,6 +333,11 @@ int cuda_convert_image(mlt_frame frame, uint8_t **image, mlt_image_format *forma
         return 1; /* another module's request */
     if (ci && resident)
         return 0; /* stays in HBM; the asking service converts on the device if it must */
+    /* the nested get_image calls below the rescale shim ask for the yuv422 the stock filter forces,
+     * on behalf of a CUDA service that asked for a resident image: leave it resident */
+    if (ci && output != mlt_image_private && mlt_properties_get_int(p, CUDA_PASSTHROUGH) > 0
+        && mlt_properties_get_int(p, CUDA_REQUESTED) > 0)
+        return 0;
 
     mlt_image_format target = output;
     if (!ci) { /* host image */
@@ -331,9 +391,17 @@ int cuda_convert_image(mlt_frame frame, uint8_t **image, mlt_image_format *forma
     return 0;
 }
 
+int cuda_convert_image(mlt_frame frame, uint8_t **image, mlt_image_format *format, mlt_image_format output)
+{
+    const uint64_t st0 = CUDA_STAT_T0();
+    int rc = cuda_convert_image_impl(frame, image, format, output);
+    CUDA_STAT_END(CS_CONVERT, st0);
+    return rc;
+}
+
 /* ---- pulling inputs ------------------------------------------------------------------------------------ */
 
-cuda_image cuda_frame_get_image(mlt_frame frame, mlt_image_format format, int *width, int *height, int writable)
+static cuda_image cuda_frame_get_image_impl(mlt_frame frame, mlt_image_format format, int *width, int *height, int writable)
 {
     mlt_properties p = MLT_FRAME_PROPERTIES(frame);
     uint8_t *img = NULL;
@@ -374,6 +442,14 @@ cuda_image cuda_frame_get_image(mlt_frame frame, mlt_image_format format, int *w
         ci = c2;
     }
     *width = ci->width, *height = ci->height;
+    return ci;
+}
+
+cuda_image cuda_frame_get_image(mlt_frame frame, mlt_image_format format, int *width, int *height, int writable)
+{
+    const uint64_t st0 = CUDA_STAT_T0();
+    cuda_image ci = cuda_frame_get_image_impl(frame, format, width, height, writable);
+    CUDA_STAT_END(CS_PULL_A, st0);
     return ci;
 }
 

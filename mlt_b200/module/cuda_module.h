@@ -28,6 +28,7 @@
 #define CUDA_IMAGE_TAG "mlt_image_private"
 #define CUDA_IMAGE_TAG_VALUE "cuda"
 #define CUDA_REQUESTED "_cuda_requested"
+#define CUDA_PASSTHROUGH "_cuda_passthrough" /* set by the rescale shim: a CUDA service is pulling through the loader's normalisers */
 #define CUDA_WORK_FORMAT "_cuda_work_format" /* format the pulling service will work in (hint for device producers) */
 
 typedef struct cuda_image_s
@@ -45,6 +46,20 @@ typedef struct cuda_image_s
 /* The calling thread's context; created on first use, worker k -> GPU k mod G.
  * NULL (and an error logged) when no device is usable: callers then fail their get_image. */
 mltcuda_ctx *cuda_thread_ctx(void);
+
+/* MLT_CUDA_STATS=1: wall time per stage, summed over the worker threads, printed at exit (stderr).
+ * Inclusive times: a transition's figure contains the get_image of its inputs. */
+enum { CS_COMPOSITE, CS_LUMA, CS_AFFINE, CS_CONVERT, CS_NOISE, CS_COLOUR, CS_DOWNLOAD, CS_UPLOAD, CS_PULL_A, CS_PULL_B, CS_SYNC, CS_N };
+extern int cuda_stats_on;
+uint64_t cuda_stat_now(void);
+void cuda_stat_add(int id, uint64_t t0);
+#define CUDA_STAT_T0() (cuda_stats_on ? cuda_stat_now() : 0)
+#define CUDA_STAT_END(id, t0) \
+    do { \
+        if (cuda_stats_on) \
+            cuda_stat_add(id, t0); \
+    } while (0)
+
 
 size_t cuda_format_bytes(mlt_image_format format, int width, int height);
 int cuda_format_supported(mlt_image_format format);
@@ -74,6 +89,11 @@ cuda_image cuda_image_convert(cuda_image src, mlt_image_format to);
 
 /* The converter callback (mlt_convert_image) the services prepend to frames. */
 int cuda_convert_image(mlt_frame frame, uint8_t **image, mlt_image_format *format, mlt_image_format output);
+
+/* filter_rescale.c: keeps device images resident through the loader's stock `rescale` normaliser */
+void cuda_rescale_install(mlt_filter stock_rescale);
+/* true if a device producer may answer this request with a resident image */
+int cuda_request_resident(mlt_frame frame, mlt_image_format requested);
 
 /* Device copy of a host uint16 luma map, cached on `owner` under `key` until the host pointer or
  * the size changes. */

@@ -110,6 +110,16 @@ static void on_producer_done(mlt_properties owner, void *unused, mlt_event_data 
     }
 }
 
+/* the loader's stock `rescale` normaliser gets the residency shim (filter_rescale.c) */
+static void on_filter_done(mlt_properties owner, void *unused, mlt_event_data ev)
+{
+    mlt_factory_event_data *d = mlt_event_data_to_object(ev);
+    if (!d || !d->name || !d->service || !*(void **) d->service || !producers_enabled())
+        return;
+    if (!strcmp(d->name, "rescale"))
+        cuda_rescale_install(*(mlt_filter *) d->service);
+}
+
 static mlt_properties metadata(mlt_service_type type, const char *id, void *data)
 {
     char file[PATH_MAX];
@@ -154,5 +164,6 @@ MLT_REPOSITORY
         mlt_events_listen(events, NULL, "transition-create-request", (mlt_listener) on_transition_request);
         mlt_events_listen(events, NULL, "filter-create-request", (mlt_listener) on_filter_request);
         mlt_events_listen(events, NULL, "producer-create-done", (mlt_listener) on_producer_done);
+        mlt_events_listen(events, NULL, "filter-create-done", (mlt_listener) on_filter_done);
     }
 }

@@ -42,15 +42,19 @@ static void copy_prop(mlt_properties dst, mlt_properties src, const char *name)
         mlt_properties_set(dst, name, mlt_properties_get(src, name));
 }
 
-static int colour_get_image(mlt_frame frame, uint8_t **buffer, mlt_image_format *format, int *width, int *height,
+static int colour_get_image_impl(mlt_frame frame, uint8_t **buffer, mlt_image_format *format, int *width, int *height,
                             int writable)
 {
     mlt_properties fp = MLT_FRAME_PROPERTIES(frame);
     mlt_producer self = mlt_frame_pop_service(frame);
     mlt_properties props = MLT_PRODUCER_PROPERTIES(self);
     const char *now = mlt_properties_get(props, "resource");
-    const int resident = *format == mlt_image_private && mlt_properties_get_int(fp, CUDA_REQUESTED) > 0;
-    const int want = mlt_properties_get_int(fp, CUDA_WORK_FORMAT);
+    const int resident = cuda_request_resident(frame, *format);
+    /* asked for a resident image directly: fill in the pulling service's working format (what the
+     * stock producer would be asked for).  Through the loader's normalisers the stock `rescale`
+     * forces yuv422 on everything below it (filter_rescale.c:221-223): make that, the puller
+     * converts on the device exactly as the reference's imageconvert would on the host. */
+    const int want = *format == mlt_image_private ? mlt_properties_get_int(fp, CUDA_WORK_FORMAT) : (int) *format;
 
     if (resident && now && strcmp(now, "checkerboard") && !mlt_properties_get(props, "mlt_image_format")
         && (want == mlt_image_yuv422 || want == mlt_image_rgba || want == mlt_image_rgba64)) {
@@ -61,6 +65,15 @@ static int colour_get_image(mlt_frame frame, uint8_t **buffer, mlt_image_format 
             *width = mlt_service_profile(MLT_PRODUCER_SERVICE(self))->width;
         if (*height <= 0)
             *height = mlt_service_profile(MLT_PRODUCER_SERVICE(self))->height;
+        /* Below the loader's rescale the request is for meta.media.width x height (the profile's
+         * size, filter_rescale.c:200-204) and the stock filter then scales that to rescale_width x
+         * rescale_height (nearest neighbour; :206-209).  A uniform picture scaled is the same uniform
+         * picture: fill at the final size, the stock filter then finds nothing to scale. */
+        if (*format != mlt_image_private && mlt_properties_get_int(fp, "rescale_width") > 0
+            && mlt_properties_get_int(fp, "rescale_height") > 0) {
+            *width = mlt_properties_get_int(fp, "rescale_width");
+            *height = mlt_properties_get_int(fp, "rescale_height");
+        }
         mlt_color c = mlt_properties_get_color(props, "resource");
         /* alpha plane exactly when the reference makes one for this format (:217-224): never merged
          * into rgba / rgba64 by the services, present for yuv422 only if the colour is translucent */
@@ -121,6 +134,14 @@ static int colour_get_image(mlt_frame frame, uint8_t **buffer, mlt_image_format 
     for (int i = 0; carry[i]; i++)
         copy_prop(fp, cfp, carry[i]);
     return 0;
+}
+
+static int colour_get_image(mlt_frame frame, uint8_t **buffer, mlt_image_format *format, int *width, int *height, int writable)
+{
+    const uint64_t st0 = CUDA_STAT_T0();
+    int rc = colour_get_image_impl(frame, buffer, format, width, height, writable);
+    CUDA_STAT_END(CS_COLOUR, st0);
+    return rc;
 }
 
 static int colour_get_frame(mlt_producer producer, mlt_frame_ptr frame, int index)

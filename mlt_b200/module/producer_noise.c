@@ -32,16 +32,15 @@ static uint32_t noise_next(noise_rng *r)
     return (r->x << 16) + (r->y & 65535u);
 }
 
-static int noise_get_image(mlt_frame frame, uint8_t **buffer, mlt_image_format *format, int *width, int *height,
+static int noise_get_image_impl(mlt_frame frame, uint8_t **buffer, mlt_image_format *format, int *width, int *height,
                            int writable)
 {
-    mlt_properties fp = MLT_FRAME_PROPERTIES(frame);
     mlt_profile profile = mlt_service_profile(MLT_PRODUCER_SERVICE(mlt_frame_get_original_producer(frame)));
     if (*width <= 0)
         *width = profile->width;
     if (*height <= 0)
         *height = profile->height;
-    const int resident = *format == mlt_image_private && mlt_properties_get_int(fp, CUDA_REQUESTED) > 0;
+    const int resident = cuda_request_resident(frame, *format);
 
     mltcuda_ctx *ctx = cuda_thread_ctx();
     if (!ctx)
@@ -63,6 +62,14 @@ static int noise_get_image(mlt_frame frame, uint8_t **buffer, mlt_image_format *
         return 0;
     /* a host filter or the consumer is asking: hand over an ordinary yuv422 image */
     return cuda_download_to_frame(frame, ci, buffer, format);
+}
+
+static int noise_get_image(mlt_frame frame, uint8_t **buffer, mlt_image_format *format, int *width, int *height, int writable)
+{
+    const uint64_t st0 = CUDA_STAT_T0();
+    int rc = noise_get_image_impl(frame, buffer, format, width, height, writable);
+    CUDA_STAT_END(CS_NOISE, st0);
+    return rc;
 }
 
 static int noise_get_audio(mlt_frame frame, int16_t **buffer, mlt_audio_format *format, int *frequency, int *channels,

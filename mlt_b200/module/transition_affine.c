@@ -160,7 +160,7 @@ static void max_output(mat3 a, double *w, double *h, double dz, double mw, doubl
     *h = (double) (y1 - y0 + 1) / mh / 2.0;
 }
 
-static int affine_get_image(mlt_frame a_frame, uint8_t **image, mlt_image_format *format, int *width, int *height,
+static int affine_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_format *format, int *width, int *height,
                             int writable)
 {
     mlt_frame b_frame = mlt_frame_pop_frame(a_frame);
@@ -354,6 +354,14 @@ out:
     /* drop the (potentially large) B image: stream-ordered free, safe after the launch */
     mlt_frame_set_image(b_frame, NULL, 0, NULL);
     mlt_properties_set(b_props, CUDA_IMAGE_TAG, NULL);
+    return rc;
+}
+
+static int affine_get_image(mlt_frame a_frame, uint8_t **image, mlt_image_format *format, int *width, int *height, int writable)
+{
+    const uint64_t st0 = CUDA_STAT_T0();
+    int rc = affine_get_image_impl(a_frame, image, format, width, height, writable);
+    CUDA_STAT_END(CS_AFFINE, st0);
     return rc;
 }
 

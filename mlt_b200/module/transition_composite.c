@@ -284,7 +284,7 @@ static uint16_t *device_luma(mlt_transition self, mltcuda_ctx *ctx, int width, i
 
 /* ---- get_image ------------------------------------------------------------------------------------ */
 
-static int composite_get_image(mlt_frame a_frame, uint8_t **image, mlt_image_format *format, int *width, int *height,
+static int composite_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_format *format, int *width, int *height,
                                int writable)
 {
     mlt_frame b_frame = mlt_frame_pop_frame(a_frame);
@@ -453,6 +453,14 @@ done:
     *image = (uint8_t *) a, *format = mlt_image_private;
     *width = a->width, *height = a->height;
     return 0;
+}
+
+static int composite_get_image(mlt_frame a_frame, uint8_t **image, mlt_image_format *format, int *width, int *height, int writable)
+{
+    const uint64_t st0 = CUDA_STAT_T0();
+    int rc = composite_get_image_impl(a_frame, image, format, width, height, writable);
+    CUDA_STAT_END(CS_COMPOSITE, st0);
+    return rc;
 }
 
 static mlt_frame composite_process(mlt_transition self, mlt_frame a_frame, mlt_frame b_frame)

@@ -133,7 +133,7 @@ static cuda_image pull_yuv422(mlt_frame frame, int via_rgba, int *w, int *h, int
     return cuda_frame_get_image(frame, mlt_image_yuv422, w, h, writable);
 }
 
-static int luma_get_image(mlt_frame a_frame, uint8_t **image, mlt_image_format *format, int *width, int *height,
+static int luma_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_format *format, int *width, int *height,
                           int writable)
 {
     mlt_frame b_frame = mlt_frame_pop_frame(a_frame);
@@ -244,6 +244,14 @@ static int luma_get_image(mlt_frame a_frame, uint8_t **image, mlt_image_format *
     *image = (uint8_t *) dst, *format = mlt_image_private;
     *width = dst->width, *height = dst->height;
     return 0;
+}
+
+static int luma_get_image(mlt_frame a_frame, uint8_t **image, mlt_image_format *format, int *width, int *height, int writable)
+{
+    const uint64_t st0 = CUDA_STAT_T0();
+    int rc = luma_get_image_impl(a_frame, image, format, width, height, writable);
+    CUDA_STAT_END(CS_LUMA, st0);
+    return rc;
 }
 
 static mlt_frame luma_process(mlt_transition self, mlt_frame a_frame, mlt_frame b_frame)
