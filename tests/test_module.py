@@ -206,3 +206,30 @@ def test_melt_renders_with_worker_threads(tmp_path):
                        env=e, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stderr[-2000:]
     assert "no usable CUDA device" not in r.stderr and "failed" not in r.stderr
+
+
+@pytest.mark.gpu
+def test_device_frames_stay_resident_through_the_loader_normalisers(tmp_path):
+    """melt attaches the loader's rescale/resize/... to every producer; the stock rescale forces yuv422 on
+    what it pulls (filter_rescale.c:221-223).  The residency shim (module/filter_rescale.c) must keep the
+    device producers' frames in HBM: no upload at all, one download per output frame."""
+    e = mltenv.env(str(tmp_path), cuda=True)
+    e["MLT_CUDA_STATS"] = "1"
+    n = 24
+    args = ["noise:", f"out={n - 1}", "-track", "noise:", f"out={n - 1}", "-transition", "composite", "a_track=0", "b_track=1",
+            "geometry=25%/25%:50%x50%:50%", "-track", "colour:0x3060c0a0", f"out={n - 1}", "-transition", "affine", "a_track=0",
+            "b_track=2", "rect=10%/10%:50%x50%:90%", "rotate_x=3"]
+    r = subprocess.run([mltenv.MELT, "-profile", "atsc_1080p_25"] + args + ["-consumer", "null", "real_time=-2", "-silent"],
+                       env=e, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    stats = {}
+    for ln in r.stderr.splitlines():
+        if ln.startswith("[cuda stats]"):
+            name, rest = ln[len("[cuda stats] "):].split("calls")
+            stats[name.strip()] = int(rest.split()[0])
+    assert stats, r.stderr[-2000:]
+    frames = stats.get("affine get_image (incl. inputs)")  # one per rendered frame
+    assert frames and frames >= n, stats
+    assert "upload" not in stats, stats
+    assert stats.get("download + sync") == frames, stats
+    assert stats.get("noise producer") == 2 * frames and stats.get("colour producer") == frames, stats

@@ -32,7 +32,7 @@ def run(cuda, frames, threads, profile, base):
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("--frames", type=int, default=2400)
+    ap.add_argument("--frames", type=int, default=12000)
     ap.add_argument("--threads", type=int, default=os.cpu_count() or 1)
     ap.add_argument("--profile", default="uhd_2160p_60")
     a = ap.parse_args()
@@ -42,7 +42,7 @@ if __name__ == "__main__":
     # 0.1 s for the stock services) and gives the steady-state rate a long timeline sees.
     short = max(8, a.frames // 12)
     for cuda in (False, True):
-        n = a.frames if cuda else max(short * 2, a.frames // 8)  # the stock arm is ~20x slower: fewer frames
+        n = a.frames if cuda else max(16, min(400, a.frames // 8))  # the stock arm is ~100x slower: fewer frames
         s0 = short if cuda else max(8, n // 6)
         _, t1 = run(cuda, s0, a.threads, a.profile, base)
         fps, t2 = run(cuda, n, a.threads, a.profile, base)
