@@ -29,7 +29,8 @@ struct CompK
     int cpr; // chunks per row upper bound
 };
 
-__global__ void __launch_bounds__(256, 8) k_composite_rows(CompK K)
+// BLIT: P.blit (SSE2 cases 0/4), a separate instantiation so the blend cases keep their exact code
+template <bool BLIT> __global__ void __launch_bounds__(256, 8) k_composite_rows(CompK K)
 {
     // grid = (chunks of a row, row, frame): no div/mod in the index math
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -46,7 +47,7 @@ __global__ void __launch_bounds__(256, 8) k_composite_rows(CompK K)
     int jlo = j0 < 0 ? 0 : j0, jhi = j0 + 8 > P.width ? P.width : j0 + 8; // valid [jlo, jhi)
     uint4 *dptr = reinterpret_cast<uint4 *>(drow + 2 * (long) j0);        // 16-byte aligned
     // a whole group of a blit (SSE2 cases 0/4: memcpy + memset) overwrites A: do not read it
-    const bool overwrite = P.blit && jlo == j0 && jhi == j0 + 8;
+    const bool overwrite = BLIT && jlo == j0 && jhi == j0 + 8;
     uint4 dv = make_uint4(0, 0, 0, 0);
     if (!overwrite)
         dv = ld16(dptr);
@@ -149,7 +150,10 @@ extern "C" int mltcuda_composite(mltcuda_ctx *ctx, const mltcuda_composite_desc 
     K.cpr = (d->width + 7 + 7) / 8; // up to 7 head pixels before the first composited pixel
     MC_BADARG(K.rows > 65535 || K.batch > 65535, "more than 65535 rows / frames in one launch");
     dim3 grd((K.cpr + 127) / 128, K.rows, K.batch);
-    k_composite_rows<<<grd, 128, 0, ctx->stream>>>(K);
+    if (K.p.blit)
+        k_composite_rows<true><<<grd, 128, 0, ctx->stream>>>(K);
+    else
+        k_composite_rows<false><<<grd, 128, 0, ctx->stream>>>(K);
     return mc_after_launch(ctx, "k_composite_rows");
 }
 
