@@ -111,11 +111,11 @@ template <typename T> __global__ void __launch_bounds__(256) k_affine(AffK K)
 // CTA's B taps share L1 lines across rows; whole groups are rejected from their two end pixels
 // (mc_affine_reject) before any A traffic; INTERP is a template parameter so only one sampler is
 // compiled into each instantiation.
-template <typename T, int INTERP> __global__ void __launch_bounds__(256) k_affine_rows(AffK K)
+template <typename T, int INTERP> __global__ void __launch_bounds__(128) k_affine_rows(AffK K)
 {
     constexpr int PPT = sizeof(T) == 1 ? 4 : 2;
     const int g = blockIdx.x * 32 + threadIdx.x;
-    const int i = blockIdx.y * 8 + threadIdx.y;
+    const int i = blockIdx.y * 4 + threadIdx.y;
     const int j = g * PPT;
     if (j >= K.a_width || i >= K.a_height)
         return;
@@ -182,7 +182,7 @@ template <typename T, int INTERP> __global__ void __launch_bounds__(256) k_affin
 template <typename T> static void launch_affine_rows(const AffK &K, int interp, cudaStream_t st)
 {
     constexpr int PPT = sizeof(T) == 1 ? 4 : 2;
-    dim3 blk(32, 8, 1), grd((K.a_width / PPT + 31) / 32, (K.a_height + 7) / 8, K.batch);
+    dim3 blk(32, 4, 1), grd((K.a_width / PPT + 31) / 32, (K.a_height + 3) / 4, K.batch);
     if (interp == MLTCUDA_INTERP_BL)
         k_affine_rows<T, 1><<<grd, blk, 0, st>>>(K);
     else if (interp == MLTCUDA_INTERP_NN)
@@ -263,7 +263,7 @@ extern "C" int mltcuda_affine(mltcuda_ctx *ctx, const mltcuda_affine_desc *d)
     const int ppt = d->format == MLTCUDA_FMT_RGBA ? 4 : 2;
     long long total = (((long long) d->a_width * d->a_height + ppt - 1) / ppt) * K.batch;
     const bool rows_ok = !K.p.degenerate && d->a_width % ppt == 0 && ((uintptr_t) d->a_image & 15) == 0 && (K.a_bs & 15) == 0
-                         && (d->a_height + 7) / 8 <= 65535 && K.batch <= 65535;
+                         && (d->a_height + 3) / 4 <= 65535 && K.batch <= 65535;
     if (rows_ok && d->format == MLTCUDA_FMT_RGBA)
         launch_affine_rows<uint8_t>(K, d->interp, ctx->stream);
     else if (rows_ok)
