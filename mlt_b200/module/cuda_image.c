@@ -27,7 +27,9 @@ mltcuda_ctx *cuda_thread_ctx(void)
     if (t_ctx || t_ctx_failed)
         return t_ctx;
     const char *dev = getenv("MLT_CUDA_DEVICE"); /* pin every worker to one GPU; default round-robin */
+    const uint64_t st0 = CUDA_STAT_T0();
     mltcuda_ctx *c = mltcuda_ctx_create(dev && *dev ? atoi(dev) : -1);
+    CUDA_STAT_END(CS_CTX_CREATE, st0);
     if (!c) {
         t_ctx_failed = 1;
         mlt_log_error(NULL, "[cuda] no usable CUDA device: %s (this module has no CPU fallback)\n", mltcuda_last_error());
@@ -50,7 +52,7 @@ int cuda_stats_on = 0;
 static _Atomic uint64_t g_stat_ns[CS_N], g_stat_calls[CS_N];
 static const char *g_stat_name[CS_N] = {"composite get_image (incl. inputs)", "luma get_image (incl. inputs)", "affine get_image (incl. inputs)",
                                         "convert_image (incl. download)", "noise producer", "colour producer", "download + sync",
-                                        "upload", "cuda_frame_get_image (pull input)", "-", "ctx sync"};
+                                        "upload", "cuda_frame_get_image (pull input)", "worker context creation", "pinned host buffer (pool)"};
 uint64_t cuda_stat_now(void)
 {
     struct timespec ts;
@@ -230,6 +232,7 @@ int cuda_download_to_frame(mlt_frame frame, cuda_image ci, uint8_t **image, mlt_
     /* pinned destination from the recycling pool: the DMA lands in the buffer the frame will own */
     uint8_t *host = mltcuda_host_pool_alloc(bytes);
     uint8_t *ahost = abytes ? mltcuda_host_pool_alloc(abytes) : NULL;
+    CUDA_STAT_END(CS_HOSTPOOL, st0);
     if (!host || (abytes && !ahost)) {
         if (host)
             mltcuda_host_pool_release(host);

@@ -49,7 +49,7 @@ mltcuda_ctx *cuda_thread_ctx(void);
 
 /* MLT_CUDA_STATS=1: wall time per stage, summed over the worker threads, printed at exit (stderr).
  * Inclusive times: a transition's figure contains the get_image of its inputs. */
-enum { CS_COMPOSITE, CS_LUMA, CS_AFFINE, CS_CONVERT, CS_NOISE, CS_COLOUR, CS_DOWNLOAD, CS_UPLOAD, CS_PULL_A, CS_PULL_B, CS_SYNC, CS_N };
+enum { CS_COMPOSITE, CS_LUMA, CS_AFFINE, CS_CONVERT, CS_NOISE, CS_COLOUR, CS_DOWNLOAD, CS_UPLOAD, CS_PULL_A, CS_CTX_CREATE, CS_HOSTPOOL, CS_N };
 extern int cuda_stats_on;
 uint64_t cuda_stat_now(void);
 void cuda_stat_add(int id, uint64_t t0);

@@ -41,7 +41,7 @@ def run(graph, frames, threads, base, extra=()):
 
 if __name__ == "__main__":
     base = tempfile.mkdtemp()
-    n0, n1 = 500, 4500
+    n0, n1 = 16, 4500
     for name, g in GRAPHS.items():
         if name == "noise only":
             continue
