@@ -325,45 +325,66 @@ __global__ void __launch_bounds__(256, (WHOLE || sizeof(T) == 2) ? 8 : 6) k_luma
         }
         uint4 a = ld16(q), s = ldg16(p);
         uint32_t aw[4] = {a.x, a.y, a.z, a.w}, sw[4] = {s.x, s.y, s.z, s.w};
+        // the per-pixel scalar chain (map weight, smoothstep, mix_a, mix_b, mix2, mix_b / mix2) runs on
+        // two pixels at once in packed fp32 (FMUL2 / FFMA2): same operations per lane
 #pragma unroll
-        for (int k = 0; k < PPT; k++) {
-            PxB<T> P, Q;
+        for (int k = 0; k < PPT; k += 2) {
+            // alpha of pixels k, k + 1: the top byte / half of each pixel
+            float2 pa, qa;
             if constexpr (sizeof(T) == 1) {
-                P.from_word(sw[k]), Q.from_word(aw[k]);
+                pa = make_float2(__uint_as_float(__byte_perm(sw[k], 0x4B000000u, 0x7543)), __uint_as_float(__byte_perm(sw[k + 1], 0x4B000000u, 0x7543)));
+                qa = make_float2(__uint_as_float(__byte_perm(aw[k], 0x4B000000u, 0x7543)), __uint_as_float(__byte_perm(aw[k + 1], 0x4B000000u, 0x7543)));
             } else {
-                P.from_word(make_uint2(sw[2 * k], sw[2 * k + 1])), Q.from_word(make_uint2(aw[2 * k], aw[2 * k + 1]));
+                pa = make_float2(__uint_as_float(__byte_perm(sw[2 * k + 1], 0x4B000000u, 0x7532)), __uint_as_float(__byte_perm(sw[2 * k + 3], 0x4B000000u, 0x7532)));
+                qa = make_float2(__uint_as_float(__byte_perm(aw[2 * k + 1], 0x4B000000u, 0x7532)), __uint_as_float(__byte_perm(aw[2 * k + 3], 0x4B000000u, 0x7532)));
             }
-            const float2 p_lo = f2_add(P.lo, unbias), p_hi = f2_add(P.hi, unbias);
-            const float2 q_lo = f2_add(Q.lo, unbias), q_hi = f2_add(Q.hi, unbias);
-            float value = K.weight;
+            pa = f2_add(pa, unbias), qa = f2_add(qa, unbias);
+            float2 value = f2_dup(K.weight);
             if (!DISSOLVE) {
-                const uint32_t lw = __ldg(lrow + (((uint32_t) (j + k) * (uint32_t) K.x_diff) >> 16));
-                const float weight = mc_fdiv_const<65535>((float) lw);
-                value = mc_smoothstep_f(weight, K.softness + weight, fpos);
+                const uint32_t l0 = __ldg(lrow + (((uint32_t) (j + k) * (uint32_t) K.x_diff) >> 16));
+                const uint32_t l1 = __ldg(lrow + (((uint32_t) (j + k + 1) * (uint32_t) K.x_diff) >> 16));
+                const float2 lf = f2_add(make_float2(__uint_as_float(0x4B000000u | l0), __uint_as_float(0x4B000000u | l1)), unbias);
+                const float2 weight = mc_fdiv_const2<65535>(lf);
+                value = mc_smoothstep_f2(weight, f2_add(f2_dup(K.softness), weight), fpos);
             }
-            const float mix_a = mc_fdiv_const<MAXI>((1.0f - value) * q_hi.y);
-            float mix_b = mc_fdiv_const<MAXI>(value * p_hi.y);
-            const float mix2 = mix_b + mix_a;
-            uint32_t o3;
+            const float2 mix_a = mc_fdiv_const2<MAXI>(f2_mul(f2_sub(f2_dup(1.0f), value), qa));
+            float2 mix_b = mc_fdiv_const2<MAXI>(f2_mul(value, pa));
+            const float2 mix2 = f2_add(mix_b, mix_a);
+            uint32_t o3[2];
             if (DISSOLVE || K.alpha_over) {
-                o3 = mc_trunc_bits(maxv * mix2);
-                if (mix2 != 0.f)
-                    mix_b = mc_fdiv_fast_rn(mix_b, mix2);
+                const uint2 oa = mc_trunc_bits_pos2(f2_mul(f2_dup(maxv), mix2));
+                o3[0] = oa.x, o3[1] = oa.y;
+                const float2 d = mc_fdiv_fast_rn2(mix_b, mix2); // NaN where mix2 == 0: not selected
+                mix_b = make_float2(mix2.x != 0.f ? d.x : mix_b.x, mix2.y != 0.f ? d.y : mix_b.y);
             } else {
-                float tt = q_hi.y + maxv * mix_b;
-                tt = tt < 0.f ? 0.f : tt > maxv ? maxv : tt;
-                o3 = mc_trunc_bits(tt);
+                float2 tt = f2_lerp(qa, mix_b, maxv); // qa + maxv * mix_b, product and sum both rounded
+                tt.x = tt.x < 0.f ? 0.f : tt.x > maxv ? maxv : tt.x;
+                tt.y = tt.y < 0.f ? 0.f : tt.y > maxv ? maxv : tt.y;
+                o3[0] = mc_trunc_bits_pos(tt.x), o3[1] = mc_trunc_bits_pos(tt.y);
             }
-            const float imix = 1.f - mix_b;
-            // p * mix_b + q * (1 - mix_b): both products rounded, then the sum
-            const float2 t_lo = f2_mul(p_lo, f2_dup(mix_b));
-            const float2 o_lo = f2_lerp(t_lo, q_lo, imix);
-            const float o_b = p_hi.x * mix_b + q_hi.x * imix;
-            if constexpr (sizeof(T) == 1) {
-                aw[k] = PxB<T>::pack(mc_trunc_bits(o_lo.x), mc_trunc_bits(o_lo.y), mc_trunc_bits(o_b), o3);
-            } else {
-                const uint2 o = PxB<T>::pack(mc_trunc_bits(o_lo.x), mc_trunc_bits(o_lo.y), mc_trunc_bits(o_b), o3);
-                aw[2 * k] = o.x, aw[2 * k + 1] = o.y;
+            const float2 imix = f2_sub(f2_dup(1.0f), mix_b);
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                PxB<T> P, Q;
+                if constexpr (sizeof(T) == 1) {
+                    P.from_word(sw[k + h]), Q.from_word(aw[k + h]);
+                } else {
+                    P.from_word(make_uint2(sw[2 * (k + h)], sw[2 * (k + h) + 1])), Q.from_word(make_uint2(aw[2 * (k + h)], aw[2 * (k + h) + 1]));
+                }
+                const float mb = h ? mix_b.y : mix_b.x, im = h ? imix.y : imix.x;
+                const float2 p_lo = f2_add(P.lo, unbias), q_lo = f2_add(Q.lo, unbias);
+                const float p_b = P.hi.x - 8388608.0f, q_b = Q.hi.x - 8388608.0f;
+                // p * mix_b + q * (1 - mix_b): both products rounded, then the sum
+                const float2 o_lo = f2_lerp(f2_mul(p_lo, f2_dup(mb)), q_lo, im);
+                const float o_b = p_b * mb + q_b * im;
+                // mixes of non-negative values with weights in [0, 1]: never negative, never NaN
+                const uint2 t_lo = mc_trunc_bits_pos2(o_lo);
+                if constexpr (sizeof(T) == 1) {
+                    aw[k + h] = PxB<T>::pack(t_lo.x, t_lo.y, mc_trunc_bits_pos(o_b), o3[h]);
+                } else {
+                    const uint2 o = PxB<T>::pack(t_lo.x, t_lo.y, mc_trunc_bits_pos(o_b), o3[h]);
+                    aw[2 * (k + h)] = o.x, aw[2 * (k + h) + 1] = o.y;
+                }
             }
         }
         *reinterpret_cast<uint4 *>(q) = make_uint4(aw[0], aw[1], aw[2], aw[3]);
