@@ -128,6 +128,71 @@ template <bool DISSOLVE> __global__ void __launch_bounds__(256, 8) k_luma_yuv422
         *dptr = make_uint4(o[0], o[1], o[2], o[3]);
         return;
     }
+    if (translucent && jlo == j0 && jhi == j0 + 8 && (!DISSOLVE || K.alpha_over)
+        && ((((uintptr_t) (ad ? ad + j0 : nullptr)) | ((uintptr_t) (as ? as + j0 : nullptr))) & 7) == 0) {
+        // translucent wipe (:417-451) / dissolve (composite_line_yuv_float :63-86) on a whole group
+        // whose alpha bytes are 8-byte aligned: vector alpha loads / stores, the per-pixel float chain
+        // on pixel pairs in packed fp32 -- the operations of the loop below, lane for lane
+        const float2 unbias = make_float2(-8388608.0f, -8388608.0f);
+        uint32_t adw[2] = {0xffffffffu, 0xffffffffu}, asw[2] = {0xffffffffu, 0xffffffffu}, aow[2];
+        if (ad) {
+            const uint2 v = ld8(ad + j0);
+            adw[0] = v.x, adw[1] = v.y;
+        }
+        if (as) {
+            const uint2 v = ld8(as + j0);
+            asw[0] = v.x, asw[1] = v.y;
+        }
+        uint8_t *at = DISSOLVE ? ad : (K.invert && as) ? as : (!K.invert && ad) ? ad : nullptr;
+        uint32_t o3[8];
+#pragma unroll
+        for (int kp = 0; kp < 4; kp++) { // pixels 2 kp, 2 kp + 1 = word kp
+            const int aw_i = (2 * kp) >> 2, ab_i = (2 * kp) & 3;
+            const float2 pa = f2_add(make_float2(__uint_as_float(__byte_perm(asw[aw_i], 0x4B000000u, 0x7540 | ab_i)),
+                                                 __uint_as_float(__byte_perm(asw[aw_i], 0x4B000000u, 0x7540 | (ab_i + 1)))), unbias);
+            const float2 qa = f2_add(make_float2(__uint_as_float(__byte_perm(adw[aw_i], 0x4B000000u, 0x7540 | ab_i)),
+                                                 __uint_as_float(__byte_perm(adw[aw_i], 0x4B000000u, 0x7540 | (ab_i + 1)))), unbias);
+            float2 value = f2_dup(K.weight);
+            if (!DISSOLVE) {
+                const uint32_t l0 = __ldg(l + (((j0 + 2 * kp) * K.x_diff) >> 16)), l1 = __ldg(l + (((j0 + 2 * kp + 1) * K.x_diff) >> 16));
+                const float2 lf = f2_add(make_float2(__uint_as_float(0x4B000000u | l0), __uint_as_float(0x4B000000u | l1)), unbias);
+                const float2 weight = mc_fdiv_const2<65535>(lf);
+                value = mc_smoothstep_f2(weight, f2_add(f2_dup(K.softness), weight), fpos);
+            }
+            const float2 mix_a = mc_fdiv_const2<255>(f2_mul(f2_sub(f2_dup(1.0f), value), qa));
+            float2 mix_b = mc_fdiv_const2<255>(f2_mul(value, pa));
+            if (at) {
+                const float2 mix2 = f2_add(mix_b, mix_a);
+                if (DISSOLVE || K.alpha_over) {
+                    const uint2 oa = mc_trunc_bits_pos2(f2_mul(f2_dup(255.0f), mix2));
+                    o3[2 * kp] = oa.x, o3[2 * kp + 1] = oa.y;
+                    const float2 q = mc_fdiv_fast_rn2(mix_b, mix2); // NaN where mix2 == 0: not selected
+                    mix_b = make_float2(mix2.x != 0.f ? q.x : mix_b.x, mix2.y != 0.f ? q.y : mix_b.y);
+                } else {
+                    float2 tt = f2_lerp(at == as ? pa : qa, mix_b, 255.0f); // at[j] + 255 * mix_b, both rounded
+                    tt.x = tt.x < 0.f ? 0.f : tt.x > 255.f ? 255.f : tt.x;
+                    tt.y = tt.y < 0.f ? 0.f : tt.y > 255.f ? 255.f : tt.y;
+                    o3[2 * kp] = mc_trunc_bits_pos(tt.x), o3[2 * kp + 1] = mc_trunc_bits_pos(tt.y);
+                }
+            }
+            const float2 imix = f2_sub(f2_dup(1.0f), mix_b);
+            const uint32_t sw = s[kp], dw = d[kp];
+            const float2 py = f2_add(make_float2(__uint_as_float(__byte_perm(sw, 0x4B000000u, 0x7540)), __uint_as_float(__byte_perm(sw, 0x4B000000u, 0x7542))), unbias);
+            const float2 pc = f2_add(make_float2(__uint_as_float(__byte_perm(sw, 0x4B000000u, 0x7541)), __uint_as_float(__byte_perm(sw, 0x4B000000u, 0x7543))), unbias);
+            const float2 qy = f2_add(make_float2(__uint_as_float(__byte_perm(dw, 0x4B000000u, 0x7540)), __uint_as_float(__byte_perm(dw, 0x4B000000u, 0x7542))), unbias);
+            const float2 qc = f2_add(make_float2(__uint_as_float(__byte_perm(dw, 0x4B000000u, 0x7541)), __uint_as_float(__byte_perm(dw, 0x4B000000u, 0x7543))), unbias);
+            // p * mix_b + q * (1 - mix_b): both products rounded, then the sum
+            const uint2 ty = mc_trunc_bits_pos2(f2_madd2r(f2_mul(py, mix_b), qy, imix));
+            const uint2 tc = mc_trunc_bits_pos2(f2_madd2r(f2_mul(pc, mix_b), qc, imix));
+            o[kp] = PxB<uint8_t>::pack(ty.x, tc.x, ty.y, tc.y);
+        }
+        *dptr = make_uint4(o[0], o[1], o[2], o[3]);
+        if (at) {
+            aow[0] = PxB<uint8_t>::pack(o3[0], o3[1], o3[2], o3[3]), aow[1] = PxB<uint8_t>::pack(o3[4], o3[5], o3[6], o3[7]);
+            *reinterpret_cast<uint2 *>(at + j0) = make_uint2(aow[0], aow[1]);
+        }
+        return;
+    }
 #pragma unroll
     for (int k = 0; k < 8; k++) {
         int j = j0 + k;

@@ -67,12 +67,12 @@ def test_no_contracted_pair_fma():
     so = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "mlt_b200", "lib", "libmltcuda_rt.so")
     sass = subprocess.run([cuobjdump, "-sass", so], capture_output=True, text=True, check=True).stdout
     assert "FADD2" in sass and "FMUL2" in sass, "packed fp32 pair ops missing: wrong build?"
-    # per kernel: FFMA2 is written on purpose only in k_luma_rgba (the packed correctly rounded divisions,
+    # per kernel: FFMA2 is written on purpose only in k_luma_rgba / k_luma_yuv422 (the packed correctly rounded divisions,
     # mc_fdiv_const2 / mc_fdiv_fast_rn2, fused in the scalar code too); anywhere else it is a contraction
     fn, bad = "", set()
     for ln in sass.splitlines():
         if "Function :" in ln:
             fn = ln.split("Function :")[1].strip()
-        elif "FFMA2" in ln and "k_luma_rgba" not in fn:
+        elif "FFMA2" in ln and "k_luma_" not in fn:
             bad.add(fn)
     assert not bad, f"a packed multiply-add pair was contracted (results would differ from the reference) in: {sorted(bad)}"

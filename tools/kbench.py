@@ -109,14 +109,19 @@ def main():
     run("K2 composite xor +alpha (scalar)", call("mltcuda_composite", comp(32768, ab=True, aa=True, op=3)), B * NPX * 9)
 
     # K3 luma
-    def luma(fmt, mapped=True, translucent=0):
+    def luma(fmt, mapped=True, translucent=0, planes=False):
         img0, img1, bs = (d_y0, d_y1, yb) if fmt == 3 else (d_r0, d_r1, rb)
         w = W if fmt != 10 else W // 2
-        return abi.LumaDesc(format=fmt, dest=img0.ptr, src=img1.ptr, map=d_map.ptr if mapped else None, luma_width=W,
+        extra = dict(alpha_dest=d_a0.ptr, alpha_src=d_a1.ptr, alpha_dest_bstride=ab_, alpha_src_bstride=ab_) if planes else {}
+        return abi.LumaDesc(**extra, format=fmt, dest=img0.ptr, src=img1.ptr, map=d_map.ptr if mapped else None, luma_width=W,
                             luma_height=H, width=w, height=H, width_dest=w, height_dest=H, width_src=w, height_src=H,
                             pos=0.4, frame_delta=0.004, softness=0.2, field_order=-1, invert=0, alpha_over=1,
                             translucent=translucent, batch=B, dest_bstride=bs, src_bstride=bs)
     run("K3 luma wipe yuv422 opaque", call("mltcuda_luma", luma(3)), B * NPX * 6 + NPX * 2)
+    run("K3 luma wipe yuv422 translucent(float, alpha planes)", call("mltcuda_luma", luma(3, translucent=1, planes=True)),
+        B * NPX * 9 + NPX * 2)
+    run("K3 dissolve yuv422 translucent(float, alpha planes)", call("mltcuda_luma", luma(3, mapped=False, translucent=1, planes=True)),
+        B * NPX * 9)
     run("K3 luma wipe rgba opaque", call("mltcuda_luma", luma(2)), B * NPX * 12 + NPX * 2)
     run("K3 luma wipe rgba64 opaque", call("mltcuda_luma", luma(10)), B * (NPX // 2) * 24 + NPX)
     run("K3 luma wipe rgba translucent(float)", call("mltcuda_luma", luma(2, translucent=1)), B * NPX * 12 + NPX * 2)
