@@ -128,6 +128,26 @@ template <bool DISSOLVE> __global__ void __launch_bounds__(256, 8) k_luma_yuv422
         *dptr = make_uint4(o[0], o[1], o[2], o[3]);
         return;
     }
+    if (DISSOLVE && !(translucent && K.alpha_over) && jlo == j0 && jhi == j0 + 8
+        && ((((uintptr_t) (ad ? ad + j0 : nullptr)) | ((uintptr_t) (as ? as + j0 : nullptr))) & 7) == 0) {
+        // cross-fade of a whole group = one composite_line_yuv group (:178-186): the composite
+        // kernel's whole-group paths (SSE2 formula / scalar), alpha planes as 8-byte vectors
+        uint32_t ab[2] = {0, 0}, aa[2] = {0, 0};
+        const uint32_t lum0[4] = {0, 0, 0, 0};
+        if (as) {
+            const uint2 v = ld8(as + j0);
+            ab[0] = v.x, ab[1] = v.y;
+        }
+        if (ad) {
+            const uint2 v = ld8(ad + j0);
+            aa[0] = v.x, aa[1] = v.y;
+        }
+        mc_composite_group8(K.cp, j0, jlo, jhi, d, s, ab, aa, lum0);
+        *dptr = make_uint4(d[0], d[1], d[2], d[3]);
+        if (ad)
+            *reinterpret_cast<uint2 *>(ad + j0) = make_uint2(aa[0], aa[1]);
+        return;
+    }
     if (translucent && jlo == j0 && jhi == j0 + 8 && (!DISSOLVE || K.alpha_over)
         && ((((uintptr_t) (ad ? ad + j0 : nullptr)) | ((uintptr_t) (as ? as + j0 : nullptr))) & 7) == 0) {
         // translucent wipe (:417-451) / dissolve (composite_line_yuv_float :63-86) on a whole group

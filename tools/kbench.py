@@ -122,6 +122,9 @@ def main():
         B * NPX * 9 + NPX * 2)
     run("K3 dissolve yuv422 translucent(float, alpha planes)", call("mltcuda_luma", luma(3, mapped=False, translucent=1, planes=True)),
         B * NPX * 9)
+    run("K3 dissolve yuv422 opaque (cross-fade)", call("mltcuda_luma", luma(3, mapped=False)), B * NPX * 6)
+    run("K3 dissolve yuv422 opaque alpha planes", call("mltcuda_luma", luma(3, mapped=False, planes=True)), B * NPX * 9)
+    run("K3 dissolve rgba opaque", call("mltcuda_luma", luma(2, mapped=False)), B * NPX * 12)
     run("K3 luma wipe rgba opaque", call("mltcuda_luma", luma(2)), B * NPX * 12 + NPX * 2)
     run("K3 luma wipe rgba64 opaque", call("mltcuda_luma", luma(10)), B * (NPX // 2) * 24 + NPX)
     run("K3 luma wipe rgba translucent(float)", call("mltcuda_luma", luma(2, translucent=1)), B * NPX * 12 + NPX * 2)
