@@ -282,6 +282,36 @@ __global__ void __launch_bounds__(256) k_yuv422_420p(CvtParams P)
     }
 }
 
+// The same for 16-pixel groups (w % 16 == 0, 16-byte aligned rows and planes): 32 bytes in, one
+// 16-byte Y store and, on the even lines, 8 + 8 chroma bytes; 2-D grid, no div/mod.
+__global__ void __launch_bounds__(256) k_yuv422_420p_v(CvtParams P)
+{
+    const int g = blockIdx.x * 32 + threadIdx.x, line = blockIdx.y * 8 + threadIdx.y;
+    const int w = P.width, h = P.height;
+    if (g >= (w >> 4) || line >= h)
+        return;
+    const int b = blockIdx.z;
+    const uint8_t *src = P.src + b * P.src_bs + (size_t) line * P.src_stride + 32 * (size_t) g;
+    uint8_t *dst = P.dst + b * P.dst_bs;
+    const uint4 a = ldg16(src), c = ldg16(src + 16);
+    const uint32_t wv[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+    uint32_t y[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        y[k] = __byte_perm(wv[2 * k], wv[2 * k + 1], 0x6420);
+    *reinterpret_cast<uint4 *>(dst + (size_t) line * w + 16 * (size_t) g) = make_uint4(y[0], y[1], y[2], y[3]);
+    if (!(line & 1) && (line >> 1) < h / 2) { // chroma of the even lines only (:352-366)
+        uint32_t t[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            t[k] = __byte_perm(wv[2 * k], wv[2 * k + 1], 0x7351); // u, u', v, v'
+        uint8_t *pu = dst + (size_t) w * h, *pv = pu + (size_t) (w / 2) * (h / 2);
+        const size_t off = (size_t) (line >> 1) * (w / 2) + 8 * (size_t) g;
+        *reinterpret_cast<uint2 *>(pu + off) = make_uint2(__byte_perm(t[0], t[1], 0x5410), __byte_perm(t[2], t[3], 0x5410));
+        *reinterpret_cast<uint2 *>(pv + off) = make_uint2(__byte_perm(t[0], t[1], 0x7632), __byte_perm(t[2], t[3], 0x7632));
+    }
+}
+
 int bytes_pp(int f)
 {
     switch (f) {
@@ -373,6 +403,12 @@ extern "C" int mltcuda_convert(mltcuda_ctx *ctx, const mltcuda_convert_desc *d)
     CELLCASE(RGBA64, YUV422, C_RGBA64_YUV422)
 #undef CELLCASE
     if (sf == MLTCUDA_FMT_YUV422 && df == MLTCUDA_FMT_YUV420P) {
+        if (aligned && d->width % 16 == 0 && P.src_stride % 16 == 0 && ((size_t) d->width * d->height) % 16 == 0
+            && (((size_t) (d->width / 2) * (d->height / 2)) % 8) == 0 && (d->height + 7) / 8 <= 65535 && P.batch <= 65535) {
+            dim3 blk(32, 8, 1), grd((d->width / 16 + 31) / 32, (d->height + 7) / 8, P.batch);
+            k_yuv422_420p_v<<<grd, blk, 0, ctx->stream>>>(P);
+            return mc_after_launch(ctx, "k_yuv422_420p_v");
+        }
         long long total = (long long) d->width * d->height * P.batch;
         k_yuv422_420p<<<mc_blocks(total, 256), 256, 0, ctx->stream>>>(P);
         return mc_after_launch(ctx, "k_yuv422_420p");

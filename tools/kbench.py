@@ -93,6 +93,18 @@ def main():
                           batch=B, src_bstride=rb, dst_bstride=yb, dst_alpha_bstride=ab_)
     run("K1 rgba->yuv422+alpha", call("mltcuda_convert", cv3), B * NPX * 7)
 
+    # the other cells of the matrix (generic pixel-pair kernel / 420p kernel); buffers reused as scratch
+    bpp = {1: 3, 2: 4, 3: 2, 4: 1.5, 10: 8}
+    for sf, df, nm in ((3, 4, "yuv422->yuv420p"), (4, 3, "yuv420p->yuv422"), (3, 1, "yuv422->rgb"), (1, 3, "rgb->yuv422"),
+                       (1, 2, "rgb->rgba"), (2, 1, "rgba->rgb"), (4, 2, "yuv420p->rgba"), (4, 1, "yuv420p->rgb"),
+                       (3, 10, "yuv422->rgba64"), (10, 3, "rgba64->yuv422"), (2, 10, "rgba->rgba64"), (10, 2, "rgba64->rgba")):
+        w = W // 2 if 10 in (sf, df) else W  # rgba64 frames are W/2 wide in the rgba-sized buffers
+        sbs, dbs = int(w * H * bpp[sf]), int(w * H * bpp[df])
+        al = dict(dst_alpha=d_a0.ptr, dst_alpha_bstride=ab_) if sf in (2, 10) and df in (1, 3) else {}
+        cvx = abi.ConvertDesc(**al, src_format=sf, dst_format=df, width=w, height=H, src=d_r1.ptr, dst=d_r0.ptr, batch=B,
+                              src_bstride=sbs, dst_bstride=dbs)
+        run(f"K1 {nm}", call("mltcuda_convert", cvx), B * (sbs + dbs))
+
     # K2 composite, full frame
     def comp(weight, ab=False, aa=False, luma=False, op=0):
         return abi.CompositeDesc(dest=d_y0.ptr, src=d_y1.ptr, alpha_b=d_a1.ptr if ab else None,
