@@ -260,6 +260,135 @@ template <int CELL> __global__ void __launch_bounds__(256) k_convert_pair(CvtPar
     }
 }
 
+// ---- vector tier of the generic cells ----------------------------------------------------------------
+// Same arithmetic as k_convert_pair, one thread = 8 pixels of a row held in registers: sources are read
+// and results written as 8 / 16-byte vectors, bytes are moved with PRMT.  Needs width % 8 == 0 (16 for
+// a yuv420p source, whose chroma rows start at ((w/2)*line)/2), 16-byte aligned images and row strides.
+__device__ __forceinline__ uint32_t lrint_div256_i(uint32_t a)
+{
+    // lrint(a / 256.0) for a < 65536, round-half-even, without the conversion pipe; low byte kept by callers
+    return (a + 127u + ((a >> 8) & 1u)) >> 8;
+}
+
+template <int CELL> __global__ void __launch_bounds__(256) k_convert_vec(CvtParams P)
+{
+    const int g = blockIdx.x * 32 + threadIdx.x, line = blockIdx.y * 8 + threadIdx.y;
+    const int w = P.width, h = P.height;
+    if (g >= (w >> 3) || line >= h)
+        return;
+    const int b = blockIdx.z;
+    const uint8_t *src = P.src + b * P.src_bs;
+    uint8_t *dst = P.dst + b * P.dst_bs;
+    const size_t x = 8 * (size_t) g;
+    constexpr bool SRC_422 = CELL == C_YUV422_RGB || CELL == C_YUV422_RGBA64;
+    constexpr bool SRC_420 = CELL == C_420_422 || CELL == C_420_RGB || CELL == C_420_RGBA;
+    constexpr bool SRC_RGB = CELL == C_RGB_YUV422 || CELL == C_RGB_RGBA;
+    constexpr bool SRC_RGBA = CELL == C_RGBA_RGB || CELL == C_RGBA_RGBA64;
+    constexpr bool SRC_RGBA64 = CELL == C_RGBA64_RGBA || CELL == C_RGBA64_YUV422;
+    constexpr bool DST_RGB = CELL == C_YUV422_RGB || CELL == C_420_RGB || CELL == C_RGBA_RGB;
+    constexpr bool DST_RGBA = CELL == C_420_RGBA || CELL == C_RGB_RGBA || CELL == C_RGBA64_RGBA;
+    constexpr bool DST_422 = CELL == C_RGB_YUV422 || CELL == C_RGBA64_YUV422;
+    constexpr bool DST_RGBA64 = CELL == C_YUV422_RGBA64 || CELL == C_RGBA_RGBA64;
+    uint32_t yuv[4] = {0, 0, 0, 0}, px[8], al[2] = {0xffffffffu, 0xffffffffu}, a16[8];
+    const bool has_sa = P.src_alpha != nullptr;
+    if (has_sa && (SRC_422 || SRC_420 || SRC_RGB)) {
+        const uint2 v = ldg8(P.src_alpha + b * P.sa_bs + (size_t) line * w + x);
+        al[0] = v.x, al[1] = v.y;
+    }
+    if (SRC_422) {
+        const uint4 v = ldg16(src + line * P.src_stride + 2 * x);
+        yuv[0] = v.x, yuv[1] = v.y, yuv[2] = v.z, yuv[3] = v.w;
+    } else if (SRC_420) { // :224-325; chroma row offset is (stride*line)/2 as written in the reference
+        const uint2 yy = ldg8(src + (size_t) w * line + x);
+        const size_t co = (size_t) (((w / 2) * line) / 2) + 4 * (size_t) g;
+        const uint32_t uu = __ldg(reinterpret_cast<const uint32_t *>(src + (size_t) w * h + co));
+        const uint32_t vv = __ldg(reinterpret_cast<const uint32_t *>(src + (size_t) w * h + (size_t) (w / 2) * (h / 2) + co));
+        const uint32_t yw[2] = {yy.x, yy.y};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t t = __byte_perm(yw[k >> 1], uu, ((k & 1) ? 0x0302 : 0x0100) | ((4 + k) << 4)); // y, u, y', -
+            yuv[k] = __byte_perm(t, vv, 0x0210 | ((4 + k) << 12));
+        }
+    } else if (SRC_RGB) {
+        const uint8_t *sp = src + line * P.src_stride + 3 * x;
+        const uint2 v0 = ldg8(sp), v1 = ldg8(sp + 8), v2 = ldg8(sp + 16);
+        const uint32_t bw[6] = {v0.x, v0.y, v1.x, v1.y, v2.x, v2.y};
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const int i = (3 * k) >> 2, o = (3 * k) & 3, i1 = i + 1 > 5 ? 5 : i + 1;
+            const uint32_t rgb = __byte_perm(bw[i], bw[i1], o | ((o + 1) << 4) | ((o + 2) << 8));
+            px[k] = __byte_perm(rgb, al[k >> 2], 0x0210 | ((4 + (k & 3)) << 12));
+        }
+    } else if (SRC_RGBA) {
+        const uint8_t *sp = src + line * P.src_stride + 4 * x;
+        const uint4 v0 = ldg16(sp), v1 = ldg16(sp + 16);
+        px[0] = v0.x, px[1] = v0.y, px[2] = v0.z, px[3] = v0.w, px[4] = v1.x, px[5] = v1.y, px[6] = v1.z, px[7] = v1.w;
+    } else if (SRC_RGBA64) {
+        const uint8_t *sp = src + line * P.src_stride + 8 * x;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint4 v = ldg16(sp + 16 * k);
+            px[2 * k] = __byte_perm(v.x, v.y, 0x7531), px[2 * k + 1] = __byte_perm(v.z, v.w, 0x7531); // high bytes
+            a16[2 * k] = v.y >> 16, a16[2 * k + 1] = v.w >> 16;
+        }
+    }
+    if (SRC_422 || (SRC_420 && CELL != C_420_422)) {
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            mc_yuyv_to_rgba2w(yuv[k], al[k >> 1], (k & 1) * 2, (k & 1) * 2 + 1, px[2 * k], px[2 * k + 1]);
+    }
+    if (CELL == C_420_422) {
+        *reinterpret_cast<uint4 *>(dst + line * P.dst_stride + 2 * x) = make_uint4(yuv[0], yuv[1], yuv[2], yuv[3]);
+    } else if (DST_RGBA) {
+        uint4 *dp = reinterpret_cast<uint4 *>(dst + line * P.dst_stride + 4 * x);
+        dp[0] = make_uint4(px[0], px[1], px[2], px[3]), dp[1] = make_uint4(px[4], px[5], px[6], px[7]);
+    } else if (DST_RGB) {
+        uint32_t ow[6];
+#pragma unroll
+        for (int m = 0; m < 6; m++) { // output bytes 4m .. 4m+3: pixel n/3, channel n%3
+            uint32_t sel = 0;
+            const int p0 = (4 * m) / 3;
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                const int n = 4 * m + t, pi = n / 3, ch = n % 3;
+                sel |= (uint32_t) ((pi - p0) * 4 + ch) << (4 * t);
+            }
+            ow[m] = __byte_perm(px[p0], px[p0 + 1 > 7 ? 7 : p0 + 1], sel);
+        }
+        uint2 *dp = reinterpret_cast<uint2 *>(dst + line * P.dst_stride + 3 * x);
+        dp[0] = make_uint2(ow[0], ow[1]), dp[1] = make_uint2(ow[2], ow[3]), dp[2] = make_uint2(ow[4], ow[5]);
+    } else if (DST_422) {
+        uint32_t y[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            y[k] = mc_rgba2_to_yuyv(px[2 * k], px[2 * k + 1]);
+        *reinterpret_cast<uint4 *>(dst + line * P.dst_stride + 2 * x) = make_uint4(y[0], y[1], y[2], y[3]);
+    } else if (DST_RGBA64) { // v * 257 = (v << 8) | v; yuv422 source: alpha a8 << 8, or 0xffff without a plane
+        const uint32_t hi_sel = (CELL == C_YUV422_RGBA64 && has_sa) ? 0x3422u : 0x3322u;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            reinterpret_cast<uint4 *>(dst + line * P.dst_stride + 8 * x)[k]
+                = make_uint4(__byte_perm(px[2 * k], 0, 0x1100), __byte_perm(px[2 * k], 0, hi_sel),
+                             __byte_perm(px[2 * k + 1], 0, 0x1100), __byte_perm(px[2 * k + 1], 0, hi_sel));
+        }
+    }
+    if ((CELL == C_RGBA_RGB || CELL == C_RGBA64_YUV422) && P.dst_alpha) { // alpha byte -> new alpha plane
+        uint32_t ao[2];
+        if (CELL == C_RGBA_RGB) {
+            ao[0] = __byte_perm(__byte_perm(px[0], px[1], 0x0073), __byte_perm(px[2], px[3], 0x0073), 0x5410);
+            ao[1] = __byte_perm(__byte_perm(px[4], px[5], 0x0073), __byte_perm(px[6], px[7], 0x0073), 0x5410);
+        } else {
+            uint32_t r[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+                r[k] = lrint_div256_i(a16[k]);
+            ao[0] = __byte_perm(__byte_perm(r[0], r[1], 0x0040), __byte_perm(r[2], r[3], 0x0040), 0x5410);
+            ao[1] = __byte_perm(__byte_perm(r[4], r[5], 0x0040), __byte_perm(r[6], r[7], 0x0040), 0x5410);
+        }
+        *reinterpret_cast<uint2 *>(P.dst_alpha + b * P.da_bs + (size_t) line * w + x) = make_uint2(ao[0], ao[1]);
+    }
+}
+
 // yuv422 -> yuv420p : filter_imageconvert.c:327-368
 __global__ void __launch_bounds__(256) k_yuv422_420p(CvtParams P)
 {
@@ -385,9 +514,20 @@ extern "C" int mltcuda_convert(mltcuda_ctx *ctx, const mltcuda_convert_desc *d)
             return mc_after_launch(ctx, "k_convert_v");
         }
     }
+    // vector tier of the other cells: tight frames, width % 8 (16 from yuv420p), aligned planes
+    const bool vec_ok = aligned && tight && d->width % (sf == MLTCUDA_FMT_YUV420P ? 16 : 8) == 0
+                        && (((uintptr_t) P.src_alpha | (uintptr_t) P.dst_alpha | P.sa_bs | P.da_bs) & 7) == 0
+                        && (d->height + 7) / 8 <= 65535 && P.batch <= 65535
+                        && (sf != MLTCUDA_FMT_YUV420P || (((size_t) d->width * d->height) % 4 == 0 && ((size_t) (d->width / 2) * (d->height / 2)) % 4 == 0));
 #define CELLCASE(S, D, C) \
-    if (sf == MLTCUDA_FMT_##S && df == MLTCUDA_FMT_##D) \
-        return launch_pair<C>(ctx, P);
+    if (sf == MLTCUDA_FMT_##S && df == MLTCUDA_FMT_##D) { \
+        if (vec_ok && C != C_YUV422_RGBA && C != C_RGBA_YUV422) { \
+            dim3 blk(32, 8, 1), grd((d->width / 8 + 31) / 32, (d->height + 7) / 8, P.batch); \
+            k_convert_vec<C><<<grd, blk, 0, ctx->stream>>>(P); \
+            return mc_after_launch(ctx, "k_convert_vec"); \
+        } \
+        return launch_pair<C>(ctx, P); \
+    }
     CELLCASE(YUV422, RGB, C_YUV422_RGB)
     CELLCASE(YUV422, RGBA, C_YUV422_RGBA)
     CELLCASE(RGB, YUV422, C_RGB_YUV422)
