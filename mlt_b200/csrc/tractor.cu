@@ -167,7 +167,7 @@ __global__ void __launch_bounds__(128, ONLY_BL ? 8 : 2) k_tractor(const __grid_c
                 fetch16(lrow + 2 * (long) j0, lrow + 2 * (long) jlo, lrow + 2 * (long) jhi, lum);
             }
             uint32_t na[2] = {al[0], al[1]};
-            mc_composite_group8(C.cp, j0, jlo, jhi, yuv, s, ab, na, lum);
+            mc_composite_group8<false>(C.cp, j0, jlo, jhi, yuv, s, ab, na, lum);
             if (has_alpha)
                 al[0] = na[0], al[1] = na[1];
         } else if (code == 4 || code == 5) {

@@ -112,6 +112,25 @@ def main():
                                  stride_dest=W * 2, stride_src=W * 2, stride_alpha_a=W, stride_alpha_b=W,
                                  weight=weight, softness=13107, step=30000, op=op, batch=B, dest_bstride=yb,
                                  src_bstride=yb, alpha_a_bstride=ab_, alpha_b_bstride=ab_, luma_bstride=0)
+    def comp_rect(weight, x, y, w, h, sx=0, ab=False, aa=False, step=1):
+        # B (its own w x h image, tightly packed from d_y1) over the rectangle (x, y, w, h) of A
+        rows = h // step
+        return abi.CompositeDesc(dest=d_y0.ptr + (y * W + x) * 2, src=d_y1.ptr + sx * 2,
+                                 alpha_b=(d_a1.ptr + sx) if ab else None, alpha_a=(d_a0.ptr + y * W + x) if aa else None,
+                                 luma=None, width=w, rows=rows, stride_dest=W * 2 * step, stride_src=w * 2 * step,
+                                 stride_alpha_a=W * step, stride_alpha_b=w * step, weight=weight, softness=0, step=0, op=0,
+                                 batch=B, dest_bstride=yb, src_bstride=yb, alpha_a_bstride=ab_, alpha_b_bstride=ab_, luma_bstride=0)
+    rw, rh = 1537, 1081
+    run("K2 composite 50% sub-rect at odd x (misaligned rows)", call("mltcuda_composite", comp_rect(32768, 101, 77, rw, rh)),
+        B * rw * rh * 6)
+    run("K2 composite 70% sub-rect odd x +alpha_a+alpha_b", call("mltcuda_composite", comp_rect(45875, 101, 77, rw, rh, ab=True, aa=True)),
+        B * rw * rh * 9)
+    run("K2 composite 50% sub-rect aligned (x=96, w=1536)", call("mltcuda_composite", comp_rect(32768, 96, 77, 1536, rh)),
+        B * 1536 * rh * 6)
+    run("K2 composite 70% sub-rect aligned +alpha_a+alpha_b", call("mltcuda_composite", comp_rect(45875, 96, 77, 1536, rh, ab=True, aa=True)),
+        B * 1536 * rh * 9)
+    run("K2 composite 50% one field (row step 2)", call("mltcuda_composite", comp_rect(32768, 0, 0, W, H, step=2)),
+        B * NPX // 2 * 6)
     run("K2 composite 50% (sse2 case1)", call("mltcuda_composite", comp(32768)), B * NPX * 6)
     run("K2 composite 70% +alpha_b (case3)", call("mltcuda_composite", comp(45875, ab=True)), B * NPX * 7)
     run("K2 composite 70% +alpha_a+alpha_b (case7)", call("mltcuda_composite", comp(45875, ab=True, aa=True)), B * NPX * 9)
