@@ -61,7 +61,7 @@ def main():
     lines = []
 
     def run(name, fn, bytes_per_launch, note=""):
-        if args.only and args.only not in name:
+        if args.only and not any(o in name for o in args.only.split("|")):
             return
         for _ in range(3):
             fn()
@@ -158,6 +158,11 @@ def main():
     run("K3 dissolve rgba opaque", call("mltcuda_luma", luma(2, mapped=False)), B * NPX * 12)
     run("K3 luma wipe rgba opaque", call("mltcuda_luma", luma(2)), B * NPX * 12 + NPX * 2)
     run("K3 luma wipe rgba64 opaque", call("mltcuda_luma", luma(10)), B * (NPX // 2) * 24 + NPX)
+    run("K3 luma wipe rgba64 translucent(float)", call("mltcuda_luma", luma(10, translucent=1)), B * (NPX // 2) * 24 + NPX)
+    run("K3 dissolve rgba64 translucent(float)", call("mltcuda_luma", luma(10, mapped=False, translucent=1)), B * (NPX // 2) * 24)
+    lf = luma(3)
+    lf.field_order = 0
+    run("K3 luma wipe yuv422 opaque, interlaced (field_order=0)", call("mltcuda_luma", lf), B * NPX * 6 + NPX * 2)
     run("K3 luma wipe rgba translucent(float)", call("mltcuda_luma", luma(2, translucent=1)), B * NPX * 12 + NPX * 2)
     run("K3 dissolve rgba translucent(float)", call("mltcuda_luma", luma(2, mapped=False, translucent=1)), B * NPX * 12)
 
@@ -187,7 +192,7 @@ def main():
         return int(((dx >= d.minima) & (dx <= d.xmax) & (dy >= d.minima) & (dy <= d.ymax)).sum()) * 16
 
     for nm, fmt, it in (("rgba bilinear", 2, 1), ("rgba nearest", 2, 0), ("rgba bicubic", 2, 2),
-                        ("rgba64 bilinear", 10, 1)):
+                        ("rgba64 bilinear", 10, 1), ("rgba64 nearest", 10, 0), ("rgba64 bicubic", 10, 2)):
         d = aff(fmt, it)
         w = W if fmt == 2 else W // 2
         cov = covered(d, w)
