@@ -103,6 +103,13 @@ int mltcuda_event_sync(mltcuda_event *ev);
  * (e.g. a frame produced on one worker's context and consumed on another's). */
 int mltcuda_ctx_wait_event(mltcuda_ctx *ctx, mltcuda_event *ev);
 float mltcuda_event_elapsed_ms(mltcuda_event *start, mltcuda_event *stop);
+/* Work submitted to `ctx` after this call starts only once everything submitted to `other` so far
+ * has completed (an event recorded on other's stream, waited on by ctx's stream; no host wait).
+ * Used when an image produced on one worker's context is read or freed by another's. */
+int mltcuda_ctx_wait_ctx(mltcuda_ctx *ctx, mltcuda_ctx *other);
+/* Copy between buffers of two contexts, possibly on different GPUs (cudaMemcpyPeerAsync), ordered
+ * after src_ctx's pending work and on dst_ctx's stream. */
+int mltcuda_copy_peer(mltcuda_ctx *dst_ctx, void *dst_dev, mltcuda_ctx *src_ctx, const void *src_dev, size_t bytes);
 
 /* ------------------------------------------------------------------------------------------ */
 /* K1  imageconvert.  Replaces the cells of conversion_matrix in
@@ -293,9 +300,21 @@ int mltcuda_noise(mltcuda_ctx *ctx, uint8_t *dst_yuv422, int width, int height, 
 int mltcuda_colour(mltcuda_ctx *ctx, void *dst, uint8_t *dst_alpha, int format, int width,
                    int height, uint8_t r, uint8_t g, uint8_t b, uint8_t a);
 
-/* Nearest-neighbour yuv422 scaler of core `rescale` (src/modules/core/filter_rescale.c:48-120). */
+/* Nearest-neighbour yuv422 scaler of core `rescale`: filter_scale
+ * (src/modules/core/filter_rescale.c:48-120).  `batch` frames per launch (bstrides in bytes). */
 int mltcuda_rescale_yuv422(mltcuda_ctx *ctx, uint8_t *dst, int dst_w, int dst_h,
-                           const uint8_t *src, int src_w, int src_h);
+                           const uint8_t *src, int src_w, int src_h,
+                           int batch, size_t dst_bstride, size_t src_bstride);
+/* Its alpha-plane companion scale_alpha (filter_rescale.c:122-147). */
+int mltcuda_rescale_alpha(mltcuda_ctx *ctx, uint8_t *dst, int dst_w, int dst_h,
+                          const uint8_t *src, int src_w, int src_h);
+/* Pad / letterbox of core `resize`: resize_image (src/modules/core/filter_resize.c:65-137) for
+ * format = YUV422 / RGBA / RGBA64 / RGB, and resize_alpha (:30-63) for a bare alpha plane
+ * (format = MLTCUDA_FMT_NONE).  The src_w x src_h input is centred in the dst_w x dst_h output;
+ * the border is black (yuv422: Y 16, UV 128) with alpha `alpha_value` (frame property
+ * "resize_alpha"). */
+int mltcuda_resize_pad(mltcuda_ctx *ctx, void *dst, int dst_w, int dst_h, const void *src, int src_w,
+                       int src_h, int format, int alpha_value);
 
 #if defined(__GNUC__)
 #pragma GCC visibility pop

@@ -106,6 +106,8 @@ SIGNATURES = {
     "mltcuda_event_record": (C.c_int, [vp, vp]),
     "mltcuda_event_sync": (C.c_int, [vp]),
     "mltcuda_ctx_wait_event": (C.c_int, [vp, vp]),
+    "mltcuda_ctx_wait_ctx": (C.c_int, [vp, vp]),
+    "mltcuda_copy_peer": (C.c_int, [vp, vp, vp, vp, sz]),
     "mltcuda_upload_staged": (C.c_int, [vp, vp, vp, C.c_size_t]),
     "mltcuda_host_pool_alloc": (vp, [C.c_size_t]),
     "mltcuda_host_pool_release": (None, [vp]),
@@ -120,7 +122,9 @@ SIGNATURES = {
     "mltcuda_tractor": (C.c_int, [vp, C.POINTER(TractorDesc)]),
     "mltcuda_noise": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, sz]),
     "mltcuda_colour": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_uint8, C.c_uint8, C.c_uint8, C.c_uint8]),
-    "mltcuda_rescale_yuv422": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, C.c_int, C.c_int]),
+    "mltcuda_rescale_yuv422": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int, sz, sz]),
+    "mltcuda_rescale_alpha": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, C.c_int, C.c_int]),
+    "mltcuda_resize_pad": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int]),
 }
 
 _lib = None

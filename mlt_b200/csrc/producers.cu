@@ -146,30 +146,83 @@ __global__ void __launch_bounds__(256) k_colour_yuv422(uint8_t *dst, int width, 
 }
 
 // filter_scale (:48-120)
-__global__ void __launch_bounds__(256) k_rescale_yuv422(uint8_t *dst, int ow, int oh, const uint8_t *src, int istride,
+// One thread = 4 output pixel pairs (16 bytes) of one row; grid = (quads of a row, row, frame).
+__global__ void __launch_bounds__(256) k_rescale_yuv422(uint8_t *dst, int ow, const uint8_t *src, int istride,
                                                         long in_middle, int scale_width, int scale_height, int outer,
-                                                        int bottom, int ncols, int nrows)
+                                                        int bottom, int ncols, size_t dst_bs, size_t src_bs)
 {
-    long long gid = (long long) blockIdx.x * blockDim.x + threadIdx.x;
-    if (gid >= (long long) ncols * nrows)
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q * 4 >= ncols)
         return;
-    int pc = (int) (gid % ncols), row = (int) (gid / ncols); // pc = output pixel pair
-    int dy = -bottom + row * scale_height;
-    int dx = -outer + 2 * pc * scale_width;
-    const uint8_t *in_line = src + in_middle + (long) (dy >> 16) * istride;
-    uint8_t *o = dst + (size_t) row * ow * 2 + 4 * (size_t) pc;
-    int base = dx >> 15;
-    base &= 0xfffffffe;
-    uint32_t r = in_line[base];
-    base &= 0xfffffffc;
-    r |= (uint32_t) in_line[base + 1] << 8;
-    dx += scale_width;
-    base = dx >> 15;
-    base &= 0xfffffffe;
-    r |= (uint32_t) in_line[base] << 16;
-    base &= 0xfffffffc;
-    r |= (uint32_t) in_line[base + 3] << 24;
-    reinterpret_cast<uint16_t *>(o)[0] = (uint16_t) r, reinterpret_cast<uint16_t *>(o)[1] = (uint16_t) (r >> 16);
+    const int row = blockIdx.y;
+    const int dy = -bottom + row * scale_height;
+    const uint8_t *in_line = src + blockIdx.z * src_bs + in_middle + (long) (dy >> 16) * istride;
+    uint8_t *o = dst + blockIdx.z * dst_bs + (size_t) row * ow * 2 + 16 * (size_t) q;
+    uint32_t r[4] = {0, 0, 0, 0};
+    const int npair = ncols - q * 4 < 4 ? ncols - q * 4 : 4;
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        if (k < npair) {
+            int dx = -outer + 2 * (q * 4 + k) * scale_width; // :97-109, two pixels per trip
+            int base = dx >> 15;
+            base &= 0xfffffffe;
+            uint32_t v = __ldg(in_line + base);
+            base &= 0xfffffffc;
+            v |= (uint32_t) __ldg(in_line + base + 1) << 8;
+            dx += scale_width;
+            base = dx >> 15;
+            base &= 0xfffffffe;
+            v |= (uint32_t) __ldg(in_line + base) << 16;
+            base &= 0xfffffffc;
+            v |= (uint32_t) __ldg(in_line + base + 3) << 24;
+            r[k] = v;
+        }
+    if (npair == 4 && ((uintptr_t) o & 15) == 0) {
+        *reinterpret_cast<uint4 *>(o) = make_uint4(r[0], r[1], r[2], r[3]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (k < npair)
+                reinterpret_cast<uint32_t *>(o)[k] = r[k]; // rows start on 4-byte boundaries (ow even)
+    }
+}
+
+// scale_alpha (filter_rescale.c:122-147): nearest neighbour sampled at the pixel centres
+__global__ void __launch_bounds__(256) k_rescale_alpha(uint8_t *dst, int ow, int oh, const uint8_t *src, int iw, int ox, int oy)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j >= ow)
+        return;
+    const int y = (oy >> 1) + i * oy, x = (ox >> 1) + j * ox;
+    dst[(size_t) i * ow + j] = __ldg(src + (size_t) (y >> 16) * iw + (x >> 16));
+}
+
+// resize_image / resize_alpha (filter_resize.c:30-137): the input centred in a frame filled with the
+// format's "nothing" (pattern = the fill bytes, period 8).  One thread = 4 output bytes.
+__global__ void __launch_bounds__(256) k_resize_pad(uint8_t *dst, int orow, int oh, const uint8_t *src, int irow, int ih,
+                                                    int off_x, int off_y, unsigned long long pattern)
+{
+    const int xb = (blockIdx.x * blockDim.x + threadIdx.x) * 4, row = blockIdx.y;
+    if (xb >= orow)
+        return;
+    const int ir = row - off_y;
+    const uint8_t *in = src + (long) ir * irow - off_x;
+    uint8_t *o = dst + (size_t) row * orow + xb;
+    uint32_t v = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int x = xb + k;
+        uint32_t byte = (uint32_t) (pattern >> (8 * (x & 7))) & 0xff;
+        if (ir >= 0 && ir < ih && x >= off_x && x < off_x + irow)
+            byte = __ldg(in + x);
+        v |= byte << (8 * k);
+    }
+    if (xb + 4 <= orow && ((uintptr_t) o & 3) == 0) {
+        *reinterpret_cast<uint32_t *>(o) = v;
+    } else {
+        for (int k = 0; k < 4 && xb + k < orow; k++)
+            o[k] = (uint8_t) (v >> (8 * k));
+    }
 }
 
 int ensure_noise_tab(mltcuda_ctx *ctx)
@@ -266,11 +319,16 @@ extern "C" int mltcuda_colour(mltcuda_ctx *ctx, void *dst, uint8_t *dst_alpha, i
     return mc_after_launch(ctx, "k_fill16");
 }
 
-extern "C" int mltcuda_rescale_yuv422(mltcuda_ctx *ctx, uint8_t *dst, int ow, int oh, const uint8_t *src, int iw, int ih)
+extern "C" int mltcuda_rescale_yuv422(mltcuda_ctx *ctx, uint8_t *dst, int ow, int oh, const uint8_t *src, int iw, int ih,
+                                      int batch, size_t dst_bstride, size_t src_bstride)
 {
     if (int e = mc_use(ctx))
         return e;
     MC_BADARG(!dst || !src || ow <= 0 || oh <= 0 || iw <= 0 || ih <= 0, "bad argument");
+    MC_BADARG((ow & 1) || ((uintptr_t) dst & 3) || (dst_bstride & 3), "rescale: even output width, 4-byte aligned destination");
+    if (batch <= 0)
+        batch = 1;
+    MC_BADARG(batch > 1 && (!dst_bstride || !src_bstride), "batch > 1 needs both bstrides");
     int istride = iw * 2;
     iw -= iw % 4;
     int out_x_range = ow / 2, out_y_range = oh / 2, in_x_range = iw / 2, in_y_range = ih / 2;
@@ -282,7 +340,59 @@ extern "C" int mltcuda_rescale_yuv422(mltcuda_ctx *ctx, uint8_t *dst, int ow, in
     // loop trip counts of :93-110: dy from -bottom step scale_height while < bottom; dx advances twice per pair
     int nrows = (2 * bottom + scale_height - 1) / scale_height;
     int ncols = (2 * outer + 2 * scale_width - 1) / (2 * scale_width);
-    k_rescale_yuv422<<<mc_blocks((long long) ncols * nrows, 256), 256, 0, ctx->stream>>>(dst, ow, oh, src, istride, in_middle,
-                                                                                     scale_width, scale_height, outer, bottom, ncols, nrows);
+    MC_BADARG(nrows > 65535 || batch > 65535, "more than 65535 rows / frames in one launch");
+    dim3 grd(mc_blocks((ncols + 3) / 4, 128), nrows, batch);
+    k_rescale_yuv422<<<grd, 128, 0, ctx->stream>>>(dst, ow, src, istride, in_middle, scale_width, scale_height, outer, bottom,
+                                                   ncols, dst_bstride, src_bstride);
     return mc_after_launch(ctx, "k_rescale_yuv422");
+}
+
+extern "C" int mltcuda_rescale_alpha(mltcuda_ctx *ctx, uint8_t *dst, int ow, int oh, const uint8_t *src, int iw, int ih)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!dst || !src || ow <= 0 || oh <= 0 || iw <= 0 || ih <= 0 || oh > 65535, "bad argument");
+    dim3 grd(mc_blocks(ow, 256), oh, 1);
+    k_rescale_alpha<<<grd, 256, 0, ctx->stream>>>(dst, ow, oh, src, iw, (iw << 16) / ow, (ih << 16) / oh);
+    return mc_after_launch(ctx, "k_rescale_alpha");
+}
+
+extern "C" int mltcuda_resize_pad(mltcuda_ctx *ctx, void *dst, int ow, int oh, const void *src, int iw, int ih, int format,
+                                  int alpha_value)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!dst || !src || ow <= 0 || oh <= 0 || iw <= 0 || ih <= 0 || iw > ow || ih > oh || oh > 65535, "bad argument");
+    int bpp;
+    unsigned long long pattern = 0;
+    const unsigned long long a = (unsigned) alpha_value & 0xff;
+    switch (format) {
+    case MLTCUDA_FMT_NONE: // a bare alpha plane (resize_alpha :30-63)
+        bpp = 1, pattern = a * 0x0101010101010101ull;
+        break;
+    case MLTCUDA_FMT_YUV422: // Y = 16, U = V = 128 (:108-114)
+        bpp = 2, pattern = 0x8010801080108010ull;
+        break;
+    case MLTCUDA_FMT_RGBA: // transparent black, alpha = resize_alpha (:90-97)
+        bpp = 4, pattern = (a << 24) | (a << 56);
+        break;
+    case MLTCUDA_FMT_RGBA64: // 16-bit alpha = alpha << 8, little endian (:98-107)
+        bpp = 8, pattern = a << 56;
+        break;
+    case MLTCUDA_FMT_RGB:
+        bpp = 3;
+        break;
+    default:
+        mltcuda_set_error("resize_pad: unsupported format %d", format);
+        return MLTCUDA_E_UNSUPPORTED;
+    }
+    int off_x = (ow - iw) / 2 * bpp, off_y = (oh - ih) / 2;
+    if (format == MLTCUDA_FMT_YUV422)
+        off_x -= off_x % 4; // keep the chroma phase (:114)
+    if (format == MLTCUDA_FMT_NONE)
+        off_x -= off_x % 2; // (:42)
+    dim3 grd(mc_blocks(((long long) ow * bpp + 3) / 4, 256), oh, 1);
+    k_resize_pad<<<grd, 256, 0, ctx->stream>>>((uint8_t *) dst, ow * bpp, oh, (const uint8_t *) src, iw * bpp, ih, off_x, off_y,
+                                               pattern);
+    return mc_after_launch(ctx, "k_resize_pad");
 }

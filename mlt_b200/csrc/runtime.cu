@@ -328,6 +328,34 @@ int mltcuda_ctx_wait_event(mltcuda_ctx *ctx, mltcuda_event *ev)
     return 0;
 }
 
+int mltcuda_ctx_wait_ctx(mltcuda_ctx *ctx, mltcuda_ctx *other)
+{
+    MC_BADARG(!ctx || !other, "null context");
+    if (ctx == other)
+        return 0;
+    if (int e = mc_use(other))
+        return e;
+    cudaEvent_t ev; // an event is cheap to create and may be destroyed while still pending
+    MC_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    cudaError_t e = cudaEventRecord(ev, other->stream);
+    if (e == cudaSuccess && (e = cudaSetDevice(ctx->device)) == cudaSuccess)
+        e = cudaStreamWaitEvent(ctx->stream, ev, 0);
+    cudaEventDestroy(ev);
+    MC_CHECK(e);
+    return 0;
+}
+
+int mltcuda_copy_peer(mltcuda_ctx *dst_ctx, void *dst, mltcuda_ctx *src_ctx, const void *src, size_t bytes)
+{
+    MC_BADARG(!dst_ctx || !src_ctx || !dst || !src, "null argument");
+    if (int e = mltcuda_ctx_wait_ctx(dst_ctx, src_ctx))
+        return e;
+    if (int e = mc_use(dst_ctx))
+        return e;
+    MC_CHECK(cudaMemcpyPeerAsync(dst, dst_ctx->device, src, src_ctx->device, bytes, dst_ctx->stream));
+    return 0;
+}
+
 int mltcuda_event_sync(mltcuda_event *ev)
 {
     MC_CHECK(cudaEventSynchronize(ev->ev));

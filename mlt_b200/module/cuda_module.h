@@ -28,18 +28,34 @@
 #define CUDA_IMAGE_TAG "mlt_image_private"
 #define CUDA_IMAGE_TAG_VALUE "cuda"
 #define CUDA_REQUESTED "_cuda_requested"
-#define CUDA_PASSTHROUGH "_cuda_passthrough" /* set by the rescale shim: a CUDA service is pulling through the loader's normalisers */
 #define CUDA_WORK_FORMAT "_cuda_work_format" /* format the pulling service will work in (hint for device producers) */
 
-typedef struct cuda_image_s
+/* Deferred op list of one image (precedent: the per-frame effect chain of
+ * src/modules/movit/filter_movit_convert.cpp:623-690).  While a CUDA service is the puller, the
+ * transitions and the converter do not launch: they append their op to the A image's list, and the
+ * list runs as ONE fused k_tractor launch (mltcuda_tractor) when somebody needs the pixels -- the
+ * converter that sees a host request, a service that uses the image as its B input, or an op the
+ * fused kernel refuses (those flush, then launch unfused). */
+typedef struct cuda_image_s *cuda_image;
+typedef struct cuda_pending_s
+{
+    mlt_image_format base_format; /* format of the buffers in `data` / `alpha` (the bottom track) */
+    int n_ops;
+    mltcuda_tractor_op ops[MLTCUDA_TRACTOR_MAX_OPS];
+    cuda_image keep[MLTCUDA_TRACTOR_MAX_OPS]; /* B images the ops read: retained until the launch */
+} cuda_pending;
+
+struct cuda_image_s
 {
     uint32_t magic;
+    int refs;              /* owners: the frame that carries the handle + pending lists that read it */
     mltcuda_ctx *ctx;      /* context (GPU + stream + pool) the buffers belong to */
-    mlt_image_format format; /* pixel format of `data`: rgb, rgba, yuv422, yuv420p, rgba64 */
+    mlt_image_format format; /* pixel format once the pending ops have run: rgb, rgba, yuv422, yuv420p, rgba64 */
     int width, height;
-    void *data;            /* device */
-    uint8_t *alpha;        /* device, 1 B/px, or NULL */
-} *cuda_image;
+    void *data;            /* device; with pending ops: the bottom track in pending->base_format */
+    uint8_t *alpha;        /* device, 1 B/px, or NULL (same remark) */
+    cuda_pending *pending; /* NULL = the buffers hold the image */
+};
 
 /* --- runtime (cuda_image.c) -------------------------------------------------------------- */
 
@@ -49,7 +65,15 @@ mltcuda_ctx *cuda_thread_ctx(void);
 
 /* MLT_CUDA_STATS=1: wall time per stage, summed over the worker threads, printed at exit (stderr).
  * Inclusive times: a transition's figure contains the get_image of its inputs. */
-enum { CS_COMPOSITE, CS_LUMA, CS_AFFINE, CS_CONVERT, CS_NOISE, CS_COLOUR, CS_DOWNLOAD, CS_UPLOAD, CS_PULL_A, CS_CTX_CREATE, CS_HOSTPOOL, CS_N };
+enum { CS_COMPOSITE, CS_LUMA, CS_AFFINE, CS_CONVERT, CS_NOISE, CS_COLOUR, CS_DOWNLOAD, CS_UPLOAD, CS_PULL_A, CS_CTX_CREATE, CS_HOSTPOOL,
+       CS_FUSED, CS_FUSED_OPS, CS_K_COMPOSITE, CS_K_AFFINE, CS_K_LUMA, CS_K_CONVERT, CS_K_RESCALE, CS_K_PAD, CS_N };
+/* count-only entries (no time): */
+void cuda_stat_count(int id, uint64_t n);
+#define CUDA_STAT_COUNT(id, n) \
+    do { \
+        if (cuda_stats_on) \
+            cuda_stat_count(id, n); \
+    } while (0)
 extern int cuda_stats_on;
 uint64_t cuda_stat_now(void);
 void cuda_stat_add(int id, uint64_t t0);
@@ -65,7 +89,26 @@ size_t cuda_format_bytes(mlt_image_format format, int width, int height);
 int cuda_format_supported(mlt_image_format format);
 
 cuda_image cuda_image_new(mltcuda_ctx *ctx, mlt_image_format format, int width, int height, int with_alpha);
-void cuda_image_close(cuda_image ci);
+void cuda_image_close(cuda_image ci); /* drops one reference */
+cuda_image cuda_image_ref(cuda_image ci);
+
+/* --- deferred op lists (cuda_image.c) -------------------------------------------------------- */
+/* Composite ops of a deferred list are built by mltcuda_composite_setup() against this fake frame
+ * pointer; cuda_image_flush() rebases them onto the output buffer. */
+#define CUDA_LAZY_BASE ((uint8_t *) (uintptr_t) 0x400000000000ull)
+/* May ops on `a` be deferred?  (MLT_CUDA_FUSE != 0, yuv422 / rgba, width % 8 == 0: what k_tractor takes) */
+int cuda_image_can_defer(cuda_image a);
+/* Append `op` (reading B image `keep`, may be NULL) to a's list.  0 on success. */
+int cuda_image_defer(cuda_image a, const mltcuda_tractor_op *op, cuda_image keep);
+/* Run a's pending ops (one fused launch) so that data / alpha hold the image.  0 on success. */
+int cuda_image_flush(cuda_image a);
+/* Will the image have an alpha plane once its pending ops have run? */
+int cuda_image_has_alpha(cuda_image a);
+/* Make `b` (materialised) readable by kernels launched on `ctx`: same context -> nothing; same GPU,
+ * other stream -> stream ordering; other GPU -> the buffers move to `ctx`.  0 on success. */
+int cuda_image_localize(cuda_image b, mltcuda_ctx *ctx);
+/* ... and after a kernel on `ctx` has read it: b's own stream must not recycle the buffers earlier. */
+void cuda_image_used_by(cuda_image b, mltcuda_ctx *ctx);
 int cuda_image_ensure_alpha(cuda_image ci, int fill); /* allocates + memsets if missing */
 void cuda_image_drop_alpha(cuda_image ci);
 
@@ -76,8 +119,13 @@ int cuda_frame_set_image(mlt_frame frame, cuda_image ci);
 
 /* Pull the frame's image as a device image in `format` (yuv422 / rgba / rgba64) at the requested
  * size (in/out like mlt_frame_get_image).  Uploads / converts on the device as needed.  The
- * returned handle stays owned by the frame.  NULL on error. */
+ * returned handle stays owned by the frame and is materialised (no pending ops): the B role.
+ * NULL on error. */
 cuda_image cuda_frame_get_image(mlt_frame frame, mlt_image_format format, int *width, int *height, int writable);
+/* The A role: the image a transition composites INTO.  May come back with pending ops (the
+ * conversion to `format` is itself deferred when it can be) and is exclusively owned by the frame
+ * (a handle that a pending list still reads is cloned first). */
+cuda_image cuda_frame_get_image_a(mlt_frame frame, mlt_image_format format, int *width, int *height);
 
 /* Replace the frame's device image `ci` by a host copy (pinned, recycled) in ci->format, with its
  * alpha plane; *image / *format are updated.  Closes the handle. */
@@ -90,8 +138,11 @@ cuda_image cuda_image_convert(cuda_image src, mlt_image_format to);
 /* The converter callback (mlt_convert_image) the services prepend to frames. */
 int cuda_convert_image(mlt_frame frame, uint8_t **image, mlt_image_format *format, mlt_image_format output);
 
-/* filter_rescale.c: keeps device images resident through the loader's stock `rescale` normaliser */
+/* filter_rescale.c: the loader's stock `rescale` / `resize` normalisers answer CUDA requests on the device */
 void cuda_rescale_install(mlt_filter stock_rescale);
+void cuda_resize_install(mlt_filter stock_resize);
+/* cuda_image.c: registers the imageconvert filter's converter on a frame (appended, like the reference) */
+void cuda_imageconvert_attach(mlt_frame frame);
 /* true if a device producer may answer this request with a resident image */
 int cuda_request_resident(mlt_frame frame, mlt_image_format requested);
 

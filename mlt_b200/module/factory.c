@@ -110,7 +110,7 @@ static void on_producer_done(mlt_properties owner, void *unused, mlt_event_data 
     }
 }
 
-/* the loader's stock `rescale` normaliser gets the residency shim (filter_rescale.c) */
+/* the loader's stock `rescale` / `resize` normalisers get their device paths (filter_rescale.c) */
 static void on_filter_done(mlt_properties owner, void *unused, mlt_event_data ev)
 {
     mlt_factory_event_data *d = mlt_event_data_to_object(ev);
@@ -118,6 +118,8 @@ static void on_filter_done(mlt_properties owner, void *unused, mlt_event_data ev
         return;
     if (!strcmp(d->name, "rescale"))
         cuda_rescale_install(*(mlt_filter *) d->service);
+    if (!strcmp(d->name, "resize"))
+        cuda_resize_install(*(mlt_filter *) d->service);
 }
 
 static mlt_properties metadata(mlt_service_type type, const char *id, void *data)

@@ -4,15 +4,17 @@
  * Drop-in for src/modules/core/filter_imageconvert.c of the reference: the filter's process()
  * registers a converter on every frame (:498-502).  Here the converter is cuda_convert_image
  * (cuda_image.c): the same conversion matrix (:423-437) evaluated by the K1 kernels, with the
- * reference's alpha-plane rules (:462-480), on device-resident or host images.  It is prepended
- * rather than appended (mlt_frame_prepend_convert_image, src/framework/mlt_frame.c:915-935) so it
- * also wins in builds where avcolor_space precedes imageconvert in core/loader.ini:10.
+ * reference's alpha-plane rules (:462-480), on device-resident or host images.  Like the reference
+ * it is APPENDED (mlt_frame_append_convert_image, :500): in a build where avcolor_space precedes
+ * imageconvert (core/loader.ini:10) that converter keeps the first try at host conversions.  The
+ * CUDA transitions additionally prepend the residency converter (cuda_convert_image), which only
+ * ever touches device-resident images.
  */
 #include "cuda_module.h"
 
 static mlt_frame imageconvert_process(mlt_filter filter, mlt_frame frame)
 {
-    mlt_frame_prepend_convert_image(frame, cuda_convert_image);
+    cuda_imageconvert_attach(frame);
     return frame;
 }
 

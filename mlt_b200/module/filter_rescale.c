@@ -1,58 +1,236 @@
-/* filter_rescale.c -- residency shim for the loader's stock `rescale` normaliser.
+/* filter_rescale.c (cuda module) -- the loader's `rescale` and `resize` normalisers on the device
+ * (SURVEY 8(f) f2).
  *
  * The loader attaches rescale + resize (+ crop, fieldorder, deinterlace) to every producer
- * (src/modules/core/loader.ini, producer_loader.c:232-248).  With its built-in scaler the stock
- * rescale filter overwrites the requested format with yuv422 before pulling its input
- * (src/modules/core/filter_rescale.c:221-223), so a device producer below it never sees the
- * mlt_image_private request of a CUDA transition: the picture was downloaded, handed up as a host
- * image and uploaded again -- two 16.6 MB PCIe trips per 2160p frame, the melt-level bottleneck.
+ * (src/modules/core/loader.ini, producer_loader.c:232-248), so they sit between every producer and
+ * every transition.  The stock filters work on host memory only: rescale overwrites the requested
+ * format with yuv422 before pulling its input (src/modules/core/filter_rescale.c:221-223) and scales
+ * with filter_scale (:48-120); resize pads whatever comes back smaller than it was asked for
+ * (filter_resize.c:143-193) -- handed a device-resident mlt_image_private picture it would "pad" the
+ * handle itself.
  *
- * The stock filter is left in place (same property bookkeeping, same scaling of host images); this
- * shim sits right above it on the frame's get_image stack.  When a CUDA service is pulling and
- * nothing above or below will touch pixels (no crop, no padding by resize), it marks the frame
- * CUDA_PASSTHROUGH for the duration of the nested call: device producers then answer the forced
- * yuv422 request with a resident yuv422 image, and cuda_convert_image leaves it resident on the
- * way back up.  Host images take the stock path unchanged.  Sizes: device producers render at the
- * requested size, so the stock filter finds nothing to scale. */
+ * Both stock filters are left in place and keep serving every host request unchanged.  This file
+ * wraps their process(): right above the entries the stock process pushes on the frame's image stack
+ * it pushes a get_image of its own.  When the request comes from one of this module's services
+ * (format mlt_image_private, "_cuda_requested" raised) that get_image discards the stock entries and
+ * does the filter's job on the device:
+ *   rescale: pulls its input as a device yuv422 image (as the stock filter forces yuv422) and scales
+ *            it with mltcuda_rescale_yuv422 / mltcuda_rescale_alpha (K6) when the sizes differ;
+ *   resize:  the aspect / letterbox arithmetic of filter_resize.c:196-298 on the host, the pad with
+ *            mltcuda_resize_pad in the format the pulling service works in.
+ * Anything else falls through to the stock get_image below.
+ */
 #include "cuda_module.h"
 
+#include <math.h>
 #include <string.h>
 
 typedef mlt_frame (*process_fn)(mlt_filter, mlt_frame);
 
-static int shim_get_image(mlt_frame frame, uint8_t **image, mlt_image_format *format, int *width, int *height, int writable)
+static int is_cuda_request(mlt_frame frame, mlt_image_format format)
 {
-    mlt_properties p = MLT_FRAME_PROPERTIES(frame);
-    int pass = *format == mlt_image_private && mlt_properties_get_int(p, CUDA_REQUESTED) > 0;
-    /* crop would cut host pixels (filter_crop.c:74-77) */
-    if (pass
-        && (mlt_properties_get_int(p, "crop.left") || mlt_properties_get_int(p, "crop.right") || mlt_properties_get_int(p, "crop.top")
-            || mlt_properties_get_int(p, "crop.bottom")))
-        pass = 0;
-    /* resize pads whatever comes back smaller than it was asked for (filter_resize.c:143-193) */
-    const int rw = mlt_properties_get_int(p, "resize_width"), rh = mlt_properties_get_int(p, "resize_height");
-    if (pass && (rw || rh) && (rw != *width || rh != *height))
-        pass = 0;
-    const int saved = mlt_properties_get_int(p, CUDA_PASSTHROUGH);
-    mlt_properties_set_int(p, CUDA_PASSTHROUGH, pass);
-    int err = mlt_frame_get_image(frame, image, format, width, height, writable); /* the stock rescale */
-    mlt_properties_set_int(p, CUDA_PASSTHROUGH, saved);
-    return err;
+    return format == mlt_image_private && mlt_properties_get_int(MLT_FRAME_PROPERTIES(frame), CUDA_REQUESTED) > 0;
 }
 
-static mlt_frame shim_process(mlt_filter filter, mlt_frame frame)
+/* drop the n entries the stock process() pushed (get_image, service, ...) */
+static void discard_stock_entries(mlt_frame frame, int n)
+{
+    while (n-- > 0)
+        mlt_deque_pop_back(MLT_FRAME_IMAGE_STACK(frame));
+}
+
+/* Run the stock process and push our get_image above whatever it pushed. */
+static mlt_frame wrap_process(mlt_filter filter, mlt_frame frame, mlt_get_image ours, int with_aspect)
 {
     process_fn stock = (process_fn) mlt_properties_get_data(MLT_FILTER_PROPERTIES(filter), "_cuda_stock_process", NULL);
+    mlt_deque stack = MLT_FRAME_IMAGE_STACK(frame);
+    const double aspect = mlt_frame_get_aspect_ratio(frame); /* what the stock resize records (:306) */
+    const int before = mlt_deque_count(stack);
     if (stock)
         frame = stock(filter, frame);
-    mlt_frame_push_get_image(frame, shim_get_image);
+    const int pushed = mlt_deque_count(stack) - before;
+    if (with_aspect)
+        mlt_deque_push_back_double(stack, aspect);
+    mlt_frame_push_service_int(frame, pushed);
+    mlt_frame_push_service(frame, filter);
+    mlt_frame_push_get_image(frame, ours);
     return frame;
 }
 
-void cuda_rescale_install(mlt_filter f)
+/* ---- rescale ------------------------------------------------------------------------------------- */
+
+static int rescale_get_image(mlt_frame frame, uint8_t **image, mlt_image_format *format, int *width, int *height, int writable)
 {
-    if (!f || !f->process || f->process == shim_process)
+    mlt_properties p = MLT_FRAME_PROPERTIES(frame);
+    mlt_filter filter = mlt_frame_pop_service(frame);
+    const int pushed = mlt_frame_pop_service_int(frame);
+    if (!is_cuda_request(frame, *format))
+        return mlt_frame_get_image(frame, image, format, width, height, writable); /* the stock rescale */
+    discard_stock_entries(frame, pushed);
+
+    mlt_properties fp = MLT_FILTER_PROPERTIES(filter);
+    if (*width == 0 || *height == 0) {
+        mlt_profile profile = mlt_service_profile(MLT_FILTER_SERVICE(filter));
+        *width = profile->width, *height = profile->height;
+    }
+    if (*width < 6 || *height < 6)
+        return 1; /* the stock filter refuses small pictures too (:186,262-264) */
+    int iw = *width, ih = *height, ow = *width, oh = *height;
+    if (mlt_properties_get(fp, "factor")) {
+        const double factor = mlt_properties_get_double(fp, "factor");
+        ow *= factor, oh *= factor;
+    }
+    const char *interps = mlt_properties_get(p, "consumer.rescale");
+    if (!interps) {
+        interps = mlt_properties_get(fp, "interpolation");
+        mlt_properties_set(p, "consumer.rescale", interps);
+    }
+    if (mlt_properties_get_int(p, "meta.media.width")) {
+        iw = mlt_properties_get_int(p, "meta.media.width");
+        ih = mlt_properties_get_int(p, "meta.media.height");
+    }
+    /* what the producer is really being asked for */
+    const int scaling = interps && strcmp(interps, "none");
+    mlt_properties_set_int(p, "rescale_width", scaling ? *width : iw);
+    mlt_properties_set_int(p, "rescale_height", scaling ? *height : ih);
+    if (ih != oh && (!interps || strcmp(interps, "nearest") || ih % oh != 0))
+        mlt_properties_set_int(p, "consumer.progressive", 1);
+
+    /* the built-in scaler works in yuv422 (:221-223): the input comes up as a device yuv422 image */
+    cuda_image ci = cuda_frame_get_image(frame, mlt_image_yuv422, &iw, &ih, writable);
+    if (!ci)
+        return 1;
+    interps = mlt_properties_get(p, "consumer.rescale"); /* the producer may have switched scaling off */
+    if (interps && strcmp(interps, "none") && (iw != ow || ih != oh)) {
+        ow -= ow % 2; /* pairs of pixels; an odd request never reaches here from resize (:279-282) */
+        cuda_image out = cuda_image_new(ci->ctx, mlt_image_yuv422, ow, oh, ci->alpha != NULL);
+        int rc = !out;
+        /* (filter_scale never writes the last row of an odd-height output: pool memory in the reference,
+         * device pool memory here) */
+        if (!rc)
+            rc = mltcuda_rescale_yuv422(ci->ctx, out->data, ow, oh, ci->data, iw, ih, 1, 0, 0);
+        if (!rc && ci->alpha)
+            rc = mltcuda_rescale_alpha(ci->ctx, out->alpha, ow, oh, ci->alpha, iw, ih);
+        CUDA_STAT_COUNT(CS_K_RESCALE, 1);
+        if (rc || cuda_frame_set_image(frame, out)) { /* takes over from ci */
+            mlt_log_error(MLT_FILTER_SERVICE(filter), "[cuda] rescale %dx%d -> %dx%d failed: %s\n", iw, ih, ow, oh,
+                          mltcuda_last_error());
+            cuda_image_close(out);
+            return 1;
+        }
+        ci = out;
+    }
+    *width = ci->width, *height = ci->height;
+    *image = (uint8_t *) ci, *format = mlt_image_private;
+    return 0;
+}
+
+static mlt_frame rescale_process(mlt_filter filter, mlt_frame frame)
+{
+    return wrap_process(filter, frame, rescale_get_image, 0);
+}
+
+/* ---- resize -------------------------------------------------------------------------------------- */
+
+static int resize_get_image(mlt_frame frame, uint8_t **image, mlt_image_format *format, int *width, int *height, int writable)
+{
+    mlt_properties p = MLT_FRAME_PROPERTIES(frame);
+    mlt_filter filter = mlt_frame_pop_service(frame);
+    const int pushed = mlt_frame_pop_service_int(frame);
+    double aspect_ratio = mlt_deque_pop_back_double(MLT_FRAME_IMAGE_STACK(frame));
+    if (!is_cuda_request(frame, *format))
+        return mlt_frame_get_image(frame, image, format, width, height, writable); /* the stock resize */
+    discard_stock_entries(frame, pushed);
+
+    mlt_profile profile = mlt_service_profile(MLT_FILTER_SERVICE(filter));
+    const double consumer_aspect = mlt_profile_sar(profile);
+    mlt_image_format work = (mlt_image_format) mlt_properties_get_int(p, CUDA_WORK_FORMAT);
+    if (work != mlt_image_rgba && work != mlt_image_rgba64 && work != mlt_image_rgb)
+        work = mlt_image_yuv422;
+    if (*width == 0 || *height == 0)
+        *width = profile->width, *height = profile->height;
+    int ow = *width, oh = *height;
+    if (aspect_ratio == 0.0)
+        aspect_ratio = consumer_aspect;
+    mlt_properties_set_double(p, "aspect_ratio", aspect_ratio);
+
+    const char *rescale = mlt_properties_get(p, "consumer.rescale");
+    const int no_scaling = rescale && !strcmp(rescale, "none");
+    if (!no_scaling) {
+        if (mlt_properties_get_int(p, "distort") == 0 && profile) {
+            /* fit the source's display aspect into the requested frame (:236-268) */
+            int real_w = mlt_properties_get_int(p, "meta.media.width"), real_h = mlt_properties_get_int(p, "meta.media.height");
+            if (real_w == 0)
+                real_w = mlt_properties_get_int(p, "width");
+            if (real_h == 0)
+                real_h = mlt_properties_get_int(p, "height");
+            const double input_ar = aspect_ratio * real_w / real_h;
+            const double output_ar = consumer_aspect * ow / oh;
+            int sw = rint((input_ar * profile->width) / output_ar), sh = profile->height;
+            if (sw > profile->width) {
+                sw = profile->width;
+                sh = rint((output_ar * profile->height) / input_ar);
+            }
+            ow = rint(sw * ow / profile->width);
+            oh = rint(sh * oh / profile->height);
+            mlt_frame_set_aspect_ratio(frame, consumer_aspect);
+        }
+        mlt_properties_set_int(p, "distort", 0);
+        mlt_properties_set_int(p, "resize_width", *width);
+        mlt_properties_set_int(p, "resize_height", *height);
+        if (work == mlt_image_yuv422) {
+            ow -= ow % 2;
+            *width -= *width % 2;
+        }
+    }
+    cuda_image ci = cuda_frame_get_image(frame, work, &ow, &oh, writable);
+    if (!ci)
+        return 1;
+    if (!no_scaling && (ci->width < *width || ci->height < *height) && ci->width <= *width && ci->height <= *height) {
+        const int has_alpha = ci->alpha != NULL && work != mlt_image_rgba; /* :176 */
+        const int alpha_value = mlt_properties_get_int(p, "resize_alpha") & 0xff;
+        cuda_image out = cuda_image_new(ci->ctx, work, *width, *height, has_alpha);
+        int rc = !out;
+        if (!rc)
+            rc = mltcuda_resize_pad(ci->ctx, out->data, *width, *height, ci->data, ci->width, ci->height, work, alpha_value);
+        if (!rc && has_alpha)
+            rc = mltcuda_resize_pad(ci->ctx, out->alpha, *width, *height, ci->alpha, ci->width, ci->height, MLTCUDA_FMT_NONE,
+                                    alpha_value);
+        CUDA_STAT_COUNT(CS_K_PAD, 1);
+        if (rc || cuda_frame_set_image(frame, out)) {
+            mlt_log_error(MLT_FILTER_SERVICE(filter), "[cuda] resize pad %dx%d -> %dx%d failed: %s\n", ci->width, ci->height,
+                          *width, *height, mltcuda_last_error());
+            cuda_image_close(out);
+            return 1;
+        }
+        ci = out;
+    }
+    *width = ci->width, *height = ci->height;
+    *image = (uint8_t *) ci, *format = mlt_image_private;
+    return 0;
+}
+
+static mlt_frame resize_process(mlt_filter filter, mlt_frame frame)
+{
+    return wrap_process(filter, frame, resize_get_image, 1);
+}
+
+/* ---- installation (factory.c: "filter-create-done") ------------------------------------------------- */
+
+static void install(mlt_filter f, process_fn ours)
+{
+    if (!f || !f->process || f->process == rescale_process || f->process == resize_process)
         return;
     mlt_properties_set_data(MLT_FILTER_PROPERTIES(f), "_cuda_stock_process", (void *) f->process, 0, NULL, NULL);
-    f->process = shim_process;
+    f->process = ours;
+}
+
+void cuda_rescale_install(mlt_filter stock_rescale)
+{
+    install(stock_rescale, rescale_process);
+}
+
+void cuda_resize_install(mlt_filter stock_resize)
+{
+    install(stock_resize, resize_process);
 }

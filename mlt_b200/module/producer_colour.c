@@ -50,10 +50,11 @@ static int colour_get_image_impl(mlt_frame frame, uint8_t **buffer, mlt_image_fo
     mlt_properties props = MLT_PRODUCER_PROPERTIES(self);
     const char *now = mlt_properties_get(props, "resource");
     const int resident = cuda_request_resident(frame, *format);
-    /* asked for a resident image directly: fill in the pulling service's working format (what the
-     * stock producer would be asked for).  Through the loader's normalisers the stock `rescale`
-     * forces yuv422 on everything below it (filter_rescale.c:221-223): make that, the puller
-     * converts on the device exactly as the reference's imageconvert would on the host. */
+    /* asked for a resident image: fill in the pulling service's working format (what the stock
+     * producer would be asked for).  Through the loader's normalisers the puller is the device
+     * `rescale` (filter_rescale.c of this module), which asks for yuv422 as the stock one does
+     * (:221-223); the transition then converts on the device exactly as the reference's imageconvert
+     * would on the host. */
     const int want = *format == mlt_image_private ? mlt_properties_get_int(fp, CUDA_WORK_FORMAT) : (int) *format;
 
     if (resident && now && strcmp(now, "checkerboard") && !mlt_properties_get(props, "mlt_image_format")
@@ -66,11 +67,10 @@ static int colour_get_image_impl(mlt_frame frame, uint8_t **buffer, mlt_image_fo
         if (*height <= 0)
             *height = mlt_service_profile(MLT_PRODUCER_SERVICE(self))->height;
         /* Below the loader's rescale the request is for meta.media.width x height (the profile's
-         * size, filter_rescale.c:200-204) and the stock filter then scales that to rescale_width x
+         * size, filter_rescale.c:200-204) and the filter then scales that to rescale_width x
          * rescale_height (nearest neighbour; :206-209).  A uniform picture scaled is the same uniform
-         * picture: fill at the final size, the stock filter then finds nothing to scale. */
-        if (*format != mlt_image_private && mlt_properties_get_int(fp, "rescale_width") > 0
-            && mlt_properties_get_int(fp, "rescale_height") > 0) {
+         * picture: fill at the final size, the rescaler then finds nothing to scale. */
+        if (mlt_properties_get_int(fp, "rescale_width") > 0 && mlt_properties_get_int(fp, "rescale_height") > 0) {
             *width = mlt_properties_get_int(fp, "rescale_width");
             *height = mlt_properties_get_int(fp, "rescale_height");
         }

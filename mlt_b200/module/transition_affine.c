@@ -168,8 +168,7 @@ static int affine_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_f
     mlt_properties props = MLT_TRANSITION_PROPERTIES(self);
     mlt_properties a_props = MLT_FRAME_PROPERTIES(a_frame), b_props = MLT_FRAME_PROPERTIES(b_frame);
     mlt_service service = MLT_TRANSITION_SERVICE(self);
-    mltcuda_ctx *ctx = cuda_thread_ctx();
-    if (!ctx)
+    if (!cuda_thread_ctx())
         return 1;
     const mlt_image_format work = *format == mlt_image_rgba64 ? mlt_image_rgba64 : mlt_image_rgba;
 
@@ -197,7 +196,7 @@ static int affine_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_f
     if (ox != 0.0 || oy != 0.0)
         *width = nw, *height = nh;
 
-    cuda_image a = cuda_frame_get_image(a_frame, work, width, height, 1);
+    cuda_image a = cuda_frame_get_image_a(a_frame, work, width, height);
     if (!a)
         return 1;
     *image = (uint8_t *) a, *format = mlt_image_private;
@@ -286,9 +285,23 @@ static int affine_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_f
     const int scale = mlt_properties_get_int(props, "scale");
     const double gsx = (double) b_width / r.w, gsy = (double) b_height / r.h;
 
+    /* launches go to the context that owns A's buffers; B is made readable from it */
+    mltcuda_ctx *ctx = a->ctx;
+    if (cuda_image_localize(b, ctx)) {
+        mlt_frame_set_image(b_frame, NULL, 0, NULL);
+        return 1;
+    }
+    /* Deferred: the transform joins A's op list and runs inside the frame's one
+     * fused k_tractor launch.  The fused kernel takes 8-bit rgba and a B image of at least 2x2;
+     * anything else (rgba64, width % 8, a degenerate B) flushes A's list and launches K4 here. */
+    const int defer = work == mlt_image_rgba && b_width >= 2 && b_height >= 2 && cuda_image_can_defer(a);
+    if (!defer && cuda_image_flush(a)) {
+        mlt_frame_set_image(b_frame, NULL, 0, NULL);
+        return 1;
+    }
     mltcuda_affine_desc d;
     memset(&d, 0, sizeof(d));
-    d.format = work, d.a_image = a->data, d.b_image = b->data, d.batch = 1;
+    d.format = work, d.a_image = defer ? NULL : a->data, d.b_image = b->data, d.batch = 1;
     d.a_width = *width, d.a_height = *height, d.b_width = b_width, d.b_height = b_height;
     d.lower_x = -(r.x + r.w / 2.0), d.lower_y = -(r.y + r.h / 2.0);
     d.mix = r.o;
@@ -346,10 +359,19 @@ static int affine_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_f
         d.interp = MLTCUDA_INTERP_BC; /* ceilf: > -1 and <= max */
         d.minima -= 1;
     }
+    if (defer) {
+        mltcuda_tractor_op top;
+        memset(&top, 0, sizeof(top));
+        top.kind = MLTCUDA_TOP_AFFINE, top.u.affine = d;
+        rc = cuda_image_defer(a, &top, b); /* the list keeps its own reference to B until it has run */
+        goto out;
+    }
+    CUDA_STAT_COUNT(CS_K_AFFINE, 1);
     if (mltcuda_affine(ctx, &d)) {
         mlt_log_error(service, "affine kernel failed: %s\n", mltcuda_last_error());
         rc = 1;
     }
+    cuda_image_used_by(b, ctx);
 out:
     /* drop the (potentially large) B image: stream-ordered free, safe after the launch */
     mlt_frame_set_image(b_frame, NULL, 0, NULL);

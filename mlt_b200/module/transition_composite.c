@@ -307,12 +307,11 @@ static int composite_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_imag
     }
     *format = mlt_image_yuv422; /* this compositor is yuv422 only (:980) */
 
-    mltcuda_ctx *ctx = cuda_thread_ctx();
-    if (!ctx)
+    if (!cuda_thread_ctx())
         return 1;
     cuda_image a = NULL, b = NULL;
     if (!b_frame) {
-        a = cuda_frame_get_image(a_frame, mlt_image_yuv422, width, height, 1);
+        a = cuda_frame_get_image_a(a_frame, mlt_image_yuv422, width, height);
         goto done;
     }
     mlt_properties a_props = MLT_FRAME_PROPERTIES(a_frame), b_props = MLT_FRAME_PROPERTIES(b_frame);
@@ -350,7 +349,7 @@ static int composite_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_imag
         b = pull_b(self, b_frame, &width_b, &height_b, &g);
         mlt_properties_set_double(a_props, "aspect_ratio", ar);
     }
-    a = cuda_frame_get_image(a_frame, mlt_image_yuv422, width, height, 1);
+    a = cuda_frame_get_image_a(a_frame, mlt_image_yuv422, width, height);
     if (!a)
         return 1;
     if (g.item.o == 0 || (g.item.w == 0 && g.item.h == 0))
@@ -383,6 +382,10 @@ static int composite_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_imag
                             || mlt_properties_get_int(props, "progressive");
     const int tff = mlt_properties_get_int(a_props, "top_field_first");
     const double softness = mlt_properties_get_double(props, "softness");
+    /* every launch below goes to the context that owns A's buffers; B is made readable from it */
+    mltcuda_ctx *ctx = a->ctx;
+    if (cuda_image_localize(b, ctx))
+        return 1;
     mlt_service_lock(service);
     uint16_t *luma = device_luma(self, ctx, width_b, height_b);
     mlt_service_unlock(service);
@@ -396,11 +399,20 @@ static int composite_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_imag
         if (!strcmp(opname, "xor"))
             op = MLTCUDA_OP_XOR;
     }
-    /* alpha plane overrides (:1098-1102) */
-    if (mlt_properties_get(props, "alpha_a") && a->alpha)
+    /* alpha plane overrides (:1098-1102): they rewrite A's plane, so A's pending ops run first */
+    if (mlt_properties_get(props, "alpha_a") && cuda_image_has_alpha(a)) {
+        if (cuda_image_flush(a))
+            return 1;
         mltcuda_memset(ctx, a->alpha, mlt_properties_get_int(props, "alpha_a"), (size_t) *width * *height);
+    }
     if (mlt_properties_get(props, "alpha_b") && b->alpha)
         mltcuda_memset(ctx, b->alpha, mlt_properties_get_int(props, "alpha_b"), (size_t) width_b * height_b);
+    /* Deferred: the blend joins A's op list and runs inside the one fused k_tractor
+     * launch of the frame.  What the fused kernel refuses (width % 8, see cuda_image_can_defer) runs
+     * here as its own K2 launch after A's list has been flushed. */
+    const int defer = cuda_image_can_defer(a);
+    if (!defer && cuda_image_flush(a))
+        return 1;
 
     for (int field = 0; field < (progressive ? 1 : 2); field++) {
         double field_position = position + field * delta * length;
@@ -439,14 +451,25 @@ static int composite_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_imag
         mltcuda_composite_desc d;
         memset(&d, 0, sizeof(d));
         d.op = op, d.batch = 1;
-        if (mltcuda_composite_setup(&d, a->data, *width, *height, b->data, width_b, height_b, b->alpha, a->alpha, &cg,
-                                    field_id, luma, softness))
+        if (mltcuda_composite_setup(&d, defer ? CUDA_LAZY_BASE : a->data, *width, *height, b->data, width_b, height_b, b->alpha,
+                                    defer ? NULL : a->alpha, &cg, field_id, luma, softness))
             continue; /* nothing visible */
+        if (defer) {
+            mltcuda_tractor_op top;
+            memset(&top, 0, sizeof(top));
+            top.kind = MLTCUDA_TOP_COMPOSITE, top.u.composite = d;
+            if (cuda_image_defer(a, &top, b))
+                return 1;
+            continue;
+        }
+        CUDA_STAT_COUNT(CS_K_COMPOSITE, 1);
         if (mltcuda_composite(ctx, &d)) {
             mlt_log_error(service, "composite kernel failed: %s\n", mltcuda_last_error());
             return 1;
         }
     }
+    if (!defer)
+        cuda_image_used_by(b, ctx);
 done:
     if (!a)
         return 1;

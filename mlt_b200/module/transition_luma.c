@@ -124,13 +124,13 @@ static mlt_producer refresh_map(mlt_transition self, mlt_frame a_frame, uint16_t
 
 /* Pull a frame as device yuv422; with fix_background_alpha the reference asks for rgba first so
  * that the conversion back creates an alpha plane (:346-367). */
-static cuda_image pull_yuv422(mlt_frame frame, int via_rgba, int *w, int *h, int writable)
+static cuda_image pull_yuv422(mlt_frame frame, int via_rgba, int *w, int *h, int a_role)
 {
     if (via_rgba && mlt_frame_has_convert_image(frame)) {
-        if (!cuda_frame_get_image(frame, mlt_image_rgba, w, h, writable))
+        if (!(a_role ? cuda_frame_get_image_a(frame, mlt_image_rgba, w, h) : cuda_frame_get_image(frame, mlt_image_rgba, w, h, 0)))
             return NULL;
     }
-    return cuda_frame_get_image(frame, mlt_image_yuv422, w, h, writable);
+    return a_role ? cuda_frame_get_image_a(frame, mlt_image_yuv422, w, h) : cuda_frame_get_image(frame, mlt_image_yuv422, w, h, 0);
 }
 
 static int luma_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_format *format, int *width, int *height,
@@ -141,8 +141,7 @@ static int luma_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_for
     mlt_properties props = MLT_TRANSITION_PROPERTIES(self);
     mlt_properties a_props = MLT_FRAME_PROPERTIES(a_frame), b_props = MLT_FRAME_PROPERTIES(b_frame);
     mlt_service service = MLT_TRANSITION_SERVICE(self);
-    mltcuda_ctx *ctx = cuda_thread_ctx();
-    if (!ctx)
+    if (!cuda_thread_ctx())
         return 1;
 
     mlt_service_lock(service);
@@ -151,9 +150,7 @@ static int luma_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_for
     if (lw == 0 || lh == 0)
         lw = *width, lh = *height;
     mlt_producer producer = refresh_map(self, a_frame, &bitmap, &lw, &lh);
-    uint16_t *dmap = NULL;
-    if (lw > 0 && lh > 0 && bitmap)
-        dmap = cuda_cached_map(props, "luma.map", ctx, bitmap, lw, lh);
+    const int have_map = lw > 0 && lh > 0 && bitmap;
 
     float mix = mlt_transition_get_progress(self, a_frame);
     float frame_delta = mlt_transition_get_progress_delta(self, a_frame);
@@ -184,14 +181,14 @@ static int luma_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_for
     d.batch = 1, d.translucent = -1; /* decided on the device like is_opaque() (:34-41) */
     d.alpha_over = alpha_over;
 
-    if (dmap) { /* luma wipe (:974-1018) */
+    if (have_map) { /* luma wipe (:974-1018) */
         reverse = invert ? !reverse : reverse;
         mix = reverse ? 1 - mix : mix;
         frame_delta *= reverse ? -1.0 : 1.0;
         dst_frame = !invert ? a_frame : b_frame, src_frame = !invert ? b_frame : a_frame;
         if (*format == mlt_image_rgba || *format == mlt_image_rgba64)
             work = *format;
-        d.map = dmap, d.luma_width = lw, d.luma_height = lh;
+        d.luma_width = lw, d.luma_height = lh;
         d.pos = mix, d.frame_delta = frame_delta, d.softness = softness;
         d.field_order = progressive ? -1 : tff;
         d.invert = invert;
@@ -211,25 +208,47 @@ static int luma_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_for
     int wd = *width, hd = *height, ws = *width, hs = *height;
     cuda_image dst, src;
     if (work == mlt_image_yuv422) {
-        if (dmap && mlt_properties_get(MLT_FRAME_PROPERTIES(dst_frame), "distort"))
+        if (have_map && mlt_properties_get(MLT_FRAME_PROPERTIES(dst_frame), "distort"))
             mlt_properties_set(MLT_FRAME_PROPERTIES(src_frame), "distort",
                                mlt_properties_get(MLT_FRAME_PROPERTIES(dst_frame), "distort"));
         dst = pull_yuv422(dst_frame, fix_bg, &wd, &hd, 1);
         src = dst ? pull_yuv422(src_frame, fix_bg, &ws, &hs, 0) : NULL;
     } else {
-        dst = cuda_frame_get_image(dst_frame, work, &wd, &hd, 1);
+        dst = cuda_frame_get_image_a(dst_frame, work, &wd, &hd);
         src = dst ? cuda_frame_get_image(src_frame, work, &ws, &hs, 0) : NULL;
     }
     if (!dst || !src) {
         rc = 1;
-    } else {
-        d.format = work, d.dest = dst->data, d.src = src->data;
-        d.alpha_dest = dst->alpha, d.alpha_src = src->alpha;
+    } else if (dst != src) {
+        /* launches go to the context that owns the destination's buffers */
+        mltcuda_ctx *ctx = dst->ctx;
+        rc = cuda_image_localize(src, ctx);
+        if (!rc && have_map && !(d.map = cuda_cached_map(props, "luma.map", ctx, bitmap, lw, lh)))
+            rc = 1;
+        d.format = work;
         d.width = *width, d.height = *height;
         d.width_dest = wd, d.height_dest = hd, d.width_src = ws, d.height_src = hs;
-        if (dst != src && mltcuda_luma(ctx, &d)) {
-            mlt_log_error(service, "Unable to dissolve incompatible images (%s)\n", mltcuda_last_error());
-            rc = 1;
+        /* Deferred: the opaque progressive yuv422 wipe joins the destination's op
+         * list (one fused k_tractor launch per frame).  Opaque is known on the host when neither
+         * image has an alpha plane (is_opaque(NULL), :34-41); everything else -- alpha planes (the
+         * float path), fields, rgba / rgba64, the dissolves -- flushes the list and launches K3. */
+        const int defer = !rc && have_map && work == mlt_image_yuv422 && d.field_order < 0 && !cuda_image_has_alpha(dst)
+                          && !src->alpha && wd == *width && hd == *height && cuda_image_can_defer(dst);
+        if (!rc && defer) {
+            mltcuda_tractor_op top;
+            memset(&top, 0, sizeof(top));
+            d.src = src->data, d.translucent = 0;
+            top.kind = MLTCUDA_TOP_LUMA, top.u.luma = d;
+            rc = cuda_image_defer(dst, &top, src);
+        } else if (!rc && !(rc = cuda_image_flush(dst))) {
+            d.dest = dst->data, d.src = src->data;
+            d.alpha_dest = dst->alpha, d.alpha_src = src->alpha;
+            CUDA_STAT_COUNT(CS_K_LUMA, 1);
+            if (mltcuda_luma(ctx, &d)) {
+                mlt_log_error(service, "Unable to dissolve incompatible images (%s)\n", mltcuda_last_error());
+                rc = 1;
+            }
+            cuda_image_used_by(src, ctx);
         }
     }
     if (producer)

@@ -411,5 +411,5 @@ def test_rescale(ctx, iw, ih, ow, oh):
     init = rnd(rng, ow * oh * 2)
     exp = oracle.rescale_yuv422(src, iw, ih, ow, oh, dst_init=init)
     d_src, d_dst = ctx.put(src), ctx.put(init)
-    abi.check(ctx.lib.mltcuda_rescale_yuv422(ctx.h, d_dst.ptr, ow, oh, d_src.ptr, iw, ih))
+    abi.check(ctx.lib.mltcuda_rescale_yuv422(ctx.h, d_dst.ptr, ow, oh, d_src.ptr, iw, ih, 1, 0, 0))
     assert np.array_equal(ctx.get(d_dst, exp.shape), exp)

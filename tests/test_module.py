@@ -131,6 +131,57 @@ EXACT = [
      A + ["-attach", f"luma:{mltenv.LUMA_PGM}", "cycle=10", "duration=6"]),
     ("imageconvert_yuv420p_out", "yuv420p", [10],
      A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=25%/25%:50%x50%:50%"]),
+    # ---- the loader's resize normaliser has to PAD (round-1 advisor finding): device-resident B whose aspect
+    # differs from the request, no mirror:flip in between -> module/filter_rescale.c pads on the device
+    ("resize_pad_colour_odd_rect", "yuv422", [0, 77],
+     A + ["-track", "colour:0x3060c0a0", "out=249", "-transition", "composite", "a_track=0", "b_track=1",
+          "geometry=0=3/5:641x355:30%; 249=-101/-33:1501x901:90%"]),
+    ("resize_pad_noise_4x3_in_16x9", "yuv422", [10],
+     A + ["-track", "noise:", "out=249", "meta.media.width=1440", "meta.media.height=1080", "-transition", "composite",
+          "a_track=0", "b_track=1", "geometry=10%/10%:60%x60%:70%"]),
+    ("resize_pad_colour_4x3_distort0", "yuv422", [10],
+     A + ["-track", "colour:0x3060c0a0", "out=249", "meta.media.width=1440", "meta.media.height=1080", "-transition",
+          "composite", "a_track=0", "b_track=1", "geometry=10%/10%:60%x60%:70%"]),
+    # device rescale: B is a resident noise picture with a fixed native size that has to be scaled down
+    ("rescale_noise_native_size", "yuv422", [10],
+     A + ["-track", "noise:", "out=249", "meta.media.width=1920", "meta.media.height=1080", "-transition", "composite",
+          "a_track=0", "b_track=1", "geometry=30%/30%:30%x30%:80%", "distort=1"]),
+    # ---- composite properties the first round never exercised against the stock service (A5)
+    ("comp_titles", "yuv422", [10],
+     A + ["-track", "colour:0x3060c0a0", "out=249", "-transition", "composite", "a_track=0", "b_track=1",
+          "geometry=10%/10%:50%x50%:70%", "titles=1"]),
+    ("comp_crop_to_fill", "yuv422", [10],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=10%/10%:30%x60%:80%", "crop_to_fill=1",
+                    "halign=centre", "valign=middle"]),
+    ("comp_fill", "yuv422", [10],
+     A + ["-track", "noise:", "out=249", "meta.media.width=720", "meta.media.height=576", "-attach", "mirror:flip", "-transition",
+          "composite", "a_track=0", "b_track=1", "geometry=5%/5%:90%x90%:80%", "fill=1"]),
+    ("comp_distort", "yuv422", [10],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=10%/10%:30%x60%:80%", "distort=1"]),
+    ("comp_deinterlace", "yuv422", [10],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=10%/10%:50%x50%:80%", "deinterlace=1"]),
+    ("comp_alpha_a_alpha_b", "yuv422", [10],
+     ["colour:0x80402060", "out=249", "-track", "colour:0x3060c0a0", "out=249", "-transition", "composite", "a_track=0",
+      "b_track=1", "geometry=10%/10%:50%x50%:70%", "alpha_a=200", "alpha_b=90"]),
+    ("comp_cycle_mirror_off", "yuv422", [0, 33, 77],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=0=0/0:50%x50%:50%; 20=50%/50%:50%x50%",
+                    "cycle=25", "mirror_off=1"]),
+    ("comp_cycle_mirror", "yuv422", [33, 77],
+     A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=0=0/0:50%x50%:50%; 20=50%/50%:50%x50%"]),
+    ("comp_and_or", "yuv422", [10],
+     ["colour:0x80402060", "out=249", "-track", "colour:0x3060c0a0", "out=249", "-transition", "composite", "a_track=0",
+      "b_track=1", "geometry=10%/10%:50%x50%:70%", "operator=and", "-track", "colour:0x10f0c040", "out=249", "-transition",
+      "composite", "a_track=0", "b_track=2", "geometry=30%/30%:50%x50%:60%", "operator=or"]),
+    # ---- the fused pass has to split: more ops than one k_tractor launch takes (MLTCUDA_TRACTOR_MAX_OPS = 8)
+    ("ten_composites", "yuv422", [5], A + sum([["-track", f"colour:0x{(i * 37) % 256:02x}{(i * 91) % 256:02x}c0{255 - i * 20:02x}", "out=249",
+                                                  "-transition", "composite", "a_track=0", f"b_track={i + 1}",
+                                                  f"geometry={3 + i * 8}%/{5 + i * 7}%:{20 + i}%x{18 + i}%:{50 + i * 5}%"]
+                                                 for i in range(10)], [])),
+    # luma wipe fused with a composite on top (one k_tractor: luma, composite)
+    ("luma_then_composite", "yuv422", [100],
+     A + NOISE_B + ["-transition", f"luma:{mltenv.LUMA_PGM}", "softness=0.2", "in=0", "out=249", "a_track=0", "b_track=1",
+                    "-track", "colour:0x3060c0a0", "out=249", "-transition", "composite", "a_track=0", "b_track=2",
+                    "geometry=10%/10%:50%x50%:70%"]),
 ]
 
 
@@ -233,3 +284,154 @@ def test_device_frames_stay_resident_through_the_loader_normalisers(tmp_path):
     assert "upload" not in stats, stats
     assert stats.get("download + sync") == frames, stats
     assert stats.get("noise producer") == 2 * frames and stats.get("colour producer") == frames, stats
+
+
+# ---- the fused tractor pass inside the module --------------------------------
+
+CFG4 = A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=5%/5%:40%x40%:80%", "-track",
+                      "colour:0x3060c0a0", "out=599", "-transition", "affine", "a_track=0", "b_track=2",
+                      "rect=0=20%/20%:50%x50%:90%; 599=30%/25%:60%x60%:70%", "rotate_x=0.5", "-track", "noise:", "out=599",
+                      "-transition", "composite", "a_track=0", "b_track=3", "geometry=55%/55%:40%x40%:100%"]
+
+
+def melt_stats(tmp_path, profile, args, frames, extra=None, workers=2):
+    e = mltenv.env(str(tmp_path), cuda=True)
+    e["MLT_CUDA_STATS"] = "1"
+    e.update(extra or {})
+    args = [a.replace("out=249", f"out={frames - 1}").replace("out=599", f"out={frames - 1}") for a in args]
+    r = subprocess.run([mltenv.MELT, "-profile", profile] + args + ["-consumer", "null", f"real_time=-{workers}", "-silent"],
+                       env=e, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    stats = {}
+    for ln in r.stderr.splitlines():
+        if ln.startswith("[cuda stats]") and "calls" in ln:
+            name, rest = ln[len("[cuda stats] "):].split("calls")
+            stats[name.strip()] = int(rest.split()[0])
+    assert stats, r.stderr[-2000:]
+    return stats, r.stderr
+
+
+@pytest.mark.gpu
+def test_cfg4_through_melt_is_one_fused_launch_per_frame(tmp_path):
+    """The drop-in defers composite / convert / affine / convert / composite onto A's op list and runs ONE
+    k_tractor per frame when the consumer asks for the host image: no k_composite_rows / k_affine launch."""
+    n = 24
+    stats, err = melt_stats(tmp_path, "uhd_2160p_60", CFG4, n)
+    frames = stats.get("download + sync")
+    assert frames and frames >= n, stats
+    assert stats.get("fused pass (k_tractor launches)") == frames, stats
+    assert stats.get("ops fused into k_tractor") == 5 * frames, stats
+    for k in ("unfused composite launches", "unfused affine launches", "unfused luma launches"):
+        assert k not in stats, stats
+    assert "compositing launches per frame" in err
+
+
+@pytest.mark.gpu
+def test_fused_and_unfused_module_paths_are_byte_identical(tmp_path):
+    fused, _ = dump(tmp_path, "fused", True, "atsc_1080p_25", "yuv422", [0, 37], CFG4)
+    unfused, _ = dump(tmp_path, "unfused", True, "atsc_1080p_25", "yuv422", [0, 37], CFG4, extra={"MLT_CUDA_FUSE": "0"})
+    for f in (0, 37):
+        assert np.array_equal(fused[f][0], unfused[f][0])
+        assert np.array_equal(fused[f][1], unfused[f][1])
+
+
+def odd_profile(tmp_path, width=1004, height=562):
+    """A profile whose width is not a multiple of 8: k_tractor refuses it (csrc/tractor.cu), the module must
+    fall back to one launch per op."""
+    p = tmp_path / "odd_profile"
+    p.write_text(f"description=test {width}x{height}\nframe_rate_num=25\nframe_rate_den=1\nwidth={width}\nheight={height}\n"
+                 "progressive=1\nsample_aspect_num=1\nsample_aspect_den=1\ndisplay_aspect_num=16\ndisplay_aspect_den=9\n"
+                 "colorspace=709\n")
+    return str(p)
+
+
+@pytest.mark.gpu
+def test_fused_pass_refusals_fall_back_to_per_op_launches(tmp_path):
+    prof = odd_profile(tmp_path)
+    # (a) width % 8 != 0: every op launches on its own, results still match the stock services
+    ref, _ = dump(tmp_path, "ref", False, prof, "yuv422", [3], CFG4)
+    got, err = dump(tmp_path, "cuda", True, prof, "yuv422", [3], CFG4)
+    diff = np.abs(ref[3][0].astype(int) - got[3][0].astype(int))
+    assert diff.max() <= 2 and (diff > 0).mean() < 1e-4
+    stats, _ = melt_stats(tmp_path, prof, CFG4, 8)
+    assert "fused pass (k_tractor launches)" not in stats, stats
+    assert stats.get("unfused composite launches") == 2 * stats["download + sync"], stats
+    assert stats.get("unfused affine launches") == stats["download + sync"], stats
+    # (b) rgba64 working format: the affine launches K4, the composites around it stay deferred
+    a64 = ["colour:0x80c04020", "out=249", "-track", "colour:0x3060c0a0", "out=249", "-transition", "affine",
+           "rect=20%/20%:50%x50%:90%", "rotate_x=0.5", "a_track=0", "b_track=1"]
+    ref, _ = dump(tmp_path, "ref64", False, "atsc_1080p_25", "rgba64", [30], a64)
+    got, _ = dump(tmp_path, "cuda64", True, "atsc_1080p_25", "rgba64", [30], a64)
+    r16, g16 = ref[30][0].view(np.uint16).astype(int), got[30][0].view(np.uint16).astype(int)
+    assert r16.shape == g16.shape and np.abs(r16 - g16).max() <= 257
+
+
+# ---- translucent (float) luma paths pinned to the compiled reference (VERDICT r1 item 4) -------------------
+
+TRANSLUCENT_B = ["-track", "colour:0x3060c0a0", "out=249"]
+LUMA_FLOAT = [
+    ("wipe_yuv422_translucent", "yuv422", [f"luma:{mltenv.LUMA_PGM}", "softness=0.2"]),
+    ("wipe_yuv422_translucent_over", "yuv422", [f"luma:{mltenv.LUMA_PGM}", "softness=0.2", "alpha_over=1"]),
+    ("dissolve_yuv422_translucent", "yuv422", ["luma"]),
+    ("dissolve_yuv422_translucent_over", "yuv422", ["luma", "alpha_over=1"]),
+    ("wipe_rgba_translucent", "rgba", [f"luma:{mltenv.LUMA_PGM}", "softness=0.2"]),
+    ("wipe_rgba_translucent_over", "rgba", [f"luma:{mltenv.LUMA_PGM}", "softness=0.2", "alpha_over=1"]),
+    ("dissolve_rgba_translucent_over", "rgba", ["luma", "alpha_over=1"]),
+    ("wipe_rgba64_translucent", "rgba64", [f"luma:{mltenv.LUMA_PGM}", "softness=0.2"]),
+    ("wipe_rgba64_translucent_over", "rgba64", [f"luma:{mltenv.LUMA_PGM}", "softness=0.2", "alpha_over=1"]),
+    ("dissolve_rgba64_translucent_over", "rgba64", ["luma", "alpha_over=1"]),
+    ("wipe_yuv422_fix_background", "yuv422", [f"luma:{mltenv.LUMA_PGM}", "softness=0.2", "fix_background_alpha=1"]),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,fmt,trans", LUMA_FLOAT, ids=[c[0] for c in LUMA_FLOAT])
+def test_translucent_luma_matches_stock_within_1lsb(tmp_path, name, fmt, trans):
+    """B = colour:0x3060c0a0 (alpha 0xa0): is_opaque() fails, the reference takes its float paths
+    (transition_luma.c:63-129,192-292,417-451,475-723).  The colour tracks are rgba64-native for the rgba64 cases."""
+    a = ["colour:0x80c04020", "out=249"] if fmt == "rgba64" else A
+    args = a + TRANSLUCENT_B + ["-transition"] + trans + ["in=0", "out=249", "a_track=0", "b_track=1"]
+    ref, _ = dump(tmp_path, "ref", False, "atsc_1080p_25", fmt, [60, 130], args)
+    got, err = dump(tmp_path, "cuda", True, "atsc_1080p_25", fmt, [60, 130], args)
+    for f in (60, 130):
+        if fmt == "rgba64":
+            r, g = ref[f][0].view(np.uint16).astype(int), got[f][0].view(np.uint16).astype(int)
+            tol = 257  # one 8-bit LSB
+        else:
+            r, g = ref[f][0].astype(int), got[f][0].astype(int)
+            tol = 1
+        assert r.shape == g.shape
+        d = np.abs(r - g)
+        print(f"{name} frame {f}: {int((d > 0).sum())} of {d.size} differ, max {int(d.max())}")
+        assert d.max() <= tol, f"frame {f}: max diff {d.max()}"
+        assert (ref[f][1] is None) == (got[f][1] is None)
+        if ref[f][1] is not None:
+            assert np.abs(ref[f][1].astype(int) - got[f][1].astype(int)).max() <= 1
+
+
+# ---- affine properties the first round never exercised against the stock service (F4) -----------------------
+
+AFFINE_PROPS = [
+    ("scale_xy", ["rect=20%/10%:60%x60%:80%", "scale_x=1.5", "scale_y=0.75"]),
+    ("invert_scale", ["rect=20%/10%:60%x60%:80%", "scale_x=1.5", "scale_y=0.75", "invert_scale=1"]),
+    ("mirror", ["rect=0=10%/10%:50%x50%:100%; 100=30%/30%:70%x70%:60%", "mirror=1", "in=0", "out=199"]),
+    ("rotate_y_z", ["rect=20%/10%:60%x60%:80%", "fix_rotate_y=25", "fix_rotate_z=-15"]),
+    ("b_scaled", ["rect=20%/10%:40%x40%:80%", "b_scaled=1"]),
+    ("fill0", ["rect=20%/10%:60%x40%:80%", "fill=0"]),
+    ("distort", ["rect=20%/10%:60%x30%:80%", "distort=1"]),
+    ("scale_flag", ["rect=20%/10%:60%x60%:80%", "fix_rotate_x=30", "scale=1"]),
+    ("cycle", ["rect=0=10%/10%:50%x50%:100%; 20=30%/30%:70%x70%:60%", "cycle=25"]),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,props", AFFINE_PROPS, ids=[c[0] for c in AFFINE_PROPS])
+def test_affine_properties_match_stock(tmp_path, name, props):
+    args = A + AFFINE_B + ["-transition", "affine"] + props + ["a_track=0", "b_track=1"]
+    frames = [30, 160]
+    ref, _ = dump(tmp_path, "ref", False, "atsc_1080p_25", "rgba", frames, args)
+    got, _ = dump(tmp_path, "cuda", True, "atsc_1080p_25", "rgba", frames, args)
+    for f in frames:
+        d = np.abs(ref[f][0].astype(int) - got[f][0].astype(int))
+        print(f"{name} frame {f}: {int((d > 0).sum())} of {d.size} differ, max {int(d.max())}")
+        assert d.max() <= 1 and (d > 0).mean() < 1e-4
