@@ -49,7 +49,7 @@ mltcuda_ctx *cuda_thread_ctx(void)
 #include <stdatomic.h>
 #include <time.h>
 int cuda_stats_on = 0;
-static _Atomic uint64_t g_stat_ns[CS_N], g_stat_calls[CS_N];
+static _Atomic uint64_t g_stat_ns[CS_N], g_stat_calls[CS_N], g_stat_bytes[CS_N];
 static const char *g_stat_name[CS_N] = {"composite get_image (incl. inputs)", "luma get_image (incl. inputs)", "affine get_image (incl. inputs)",
                                         "convert_image (incl. download)", "noise producer", "colour producer", "download + sync",
                                         "upload", "cuda_frame_get_image (pull input)", "worker context creation", "pinned host buffer (pool)",
@@ -71,12 +71,17 @@ void cuda_stat_count(int id, uint64_t n)
 {
     atomic_fetch_add(&g_stat_calls[id], n);
 }
+void cuda_stat_bytes(int id, uint64_t n)
+{
+    atomic_fetch_add(&g_stat_bytes[id], n);
+}
 static void cuda_stats_print(void)
 {
     for (int i = 0; i < CS_N; i++)
         if (g_stat_calls[i])
-            fprintf(stderr, "[cuda stats] %-36s calls %8llu  total %9.1f ms  mean %8.1f us\n", g_stat_name[i],
-                    (unsigned long long) g_stat_calls[i], g_stat_ns[i] / 1e6, g_stat_ns[i] / 1e3 / g_stat_calls[i]);
+            fprintf(stderr, "[cuda stats] %-36s calls %8llu  total %9.1f ms  mean %8.1f us  bytes %llu\n", g_stat_name[i],
+                    (unsigned long long) g_stat_calls[i], g_stat_ns[i] / 1e6, g_stat_ns[i] / 1e3 / g_stat_calls[i],
+                    (unsigned long long) g_stat_bytes[i]);
     /* every kernel the worker contexts launched (producers included), per downloaded frame */
     unsigned long long launches = 0;
     pthread_mutex_lock(&g_ctx_lock);
@@ -421,6 +426,8 @@ static cuda_image upload_host_image(mlt_frame frame, mltcuda_ctx *ctx, const uin
     const uint64_t st0 = CUDA_STAT_T0();
     cuda_image ci = upload_host_image_impl(frame, ctx, image, format, width, height);
     CUDA_STAT_END(CS_UPLOAD, st0);
+    if (cuda_stats_on && ci)
+        cuda_stat_bytes(CS_UPLOAD, cuda_format_bytes(format, width, height) + (ci->alpha ? (size_t) width * height : 0));
     return ci;
 }
 
@@ -449,6 +456,8 @@ int cuda_download_to_frame(mlt_frame frame, cuda_image ci, uint8_t **image, mlt_
     if (!rc)
         rc = mltcuda_ctx_sync(ci->ctx);
     CUDA_STAT_END(CS_DOWNLOAD, st0);
+    if (cuda_stats_on)
+        cuda_stat_bytes(CS_DOWNLOAD, bytes + abytes);
     if (rc) {
         mlt_log_error(NULL, "[cuda] download failed: %s\n", mltcuda_last_error());
         if (host)

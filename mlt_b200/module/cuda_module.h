@@ -69,6 +69,7 @@ enum { CS_COMPOSITE, CS_LUMA, CS_AFFINE, CS_CONVERT, CS_NOISE, CS_COLOUR, CS_DOW
        CS_FUSED, CS_FUSED_OPS, CS_K_COMPOSITE, CS_K_AFFINE, CS_K_LUMA, CS_K_CONVERT, CS_K_RESCALE, CS_K_PAD, CS_N };
 /* count-only entries (no time): */
 void cuda_stat_count(int id, uint64_t n);
+void cuda_stat_bytes(int id, uint64_t n);
 #define CUDA_STAT_COUNT(id, n) \
     do { \
         if (cuda_stats_on) \

@@ -207,7 +207,14 @@ static int luma_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_for
 
     int wd = *width, hd = *height, ws = *width, hs = *height;
     cuda_image dst, src;
+    /* Reference quirk: with fix_background_alpha the frames are pulled as rgba and converted back with
+     * a bare mlt_frame_convert_image (:361-367,150-160), which leaves the frame's "format" property at
+     * rgba -- and mlt_frame_get_alpha() answers NULL for rgba frames (mlt_frame.c:551-564).  The alpha
+     * planes the conversion created are therefore invisible to the blend: integer path, planes untouched. */
+    int hide_alpha_dst = 0, hide_alpha_src = 0;
     if (work == mlt_image_yuv422) {
+        hide_alpha_dst = fix_bg && mlt_frame_has_convert_image(dst_frame);
+        hide_alpha_src = fix_bg && mlt_frame_has_convert_image(src_frame);
         if (have_map && mlt_properties_get(MLT_FRAME_PROPERTIES(dst_frame), "distort"))
             mlt_properties_set(MLT_FRAME_PROPERTIES(src_frame), "distort",
                                mlt_properties_get(MLT_FRAME_PROPERTIES(dst_frame), "distort"));
@@ -232,8 +239,9 @@ static int luma_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_for
          * list (one fused k_tractor launch per frame).  Opaque is known on the host when neither
          * image has an alpha plane (is_opaque(NULL), :34-41); everything else -- alpha planes (the
          * float path), fields, rgba / rgba64, the dissolves -- flushes the list and launches K3. */
-        const int defer = !rc && have_map && work == mlt_image_yuv422 && d.field_order < 0 && !cuda_image_has_alpha(dst)
-                          && !src->alpha && wd == *width && hd == *height && cuda_image_can_defer(dst);
+        const int defer = !rc && have_map && work == mlt_image_yuv422 && d.field_order < 0
+                          && (hide_alpha_dst || !cuda_image_has_alpha(dst)) && (hide_alpha_src || !src->alpha) && wd == *width
+                          && hd == *height && cuda_image_can_defer(dst);
         if (!rc && defer) {
             mltcuda_tractor_op top;
             memset(&top, 0, sizeof(top));
@@ -242,7 +250,7 @@ static int luma_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_for
             rc = cuda_image_defer(dst, &top, src);
         } else if (!rc && !(rc = cuda_image_flush(dst))) {
             d.dest = dst->data, d.src = src->data;
-            d.alpha_dest = dst->alpha, d.alpha_src = src->alpha;
+            d.alpha_dest = hide_alpha_dst ? NULL : dst->alpha, d.alpha_src = hide_alpha_src ? NULL : src->alpha;
             CUDA_STAT_COUNT(CS_K_LUMA, 1);
             if (mltcuda_luma(ctx, &d)) {
                 mlt_log_error(service, "Unable to dissolve incompatible images (%s)\n", mltcuda_last_error());

@@ -173,9 +173,11 @@ EXACT = [
       "b_track=1", "geometry=10%/10%:50%x50%:70%", "operator=and", "-track", "colour:0x10f0c040", "out=249", "-transition",
       "composite", "a_track=0", "b_track=2", "geometry=30%/30%:50%x50%:60%", "operator=or"]),
     # ---- the fused pass has to split: more ops than one k_tractor launch takes (MLTCUDA_TRACTOR_MAX_OPS = 8)
+    # (rectangles are 16:9 with even heights: the reference's nearest scaler never writes the last row of an
+    # odd-height output, filter_rescale.c:93 -- pool garbage no implementation can reproduce)
     ("ten_composites", "yuv422", [5], A + sum([["-track", f"colour:0x{(i * 37) % 256:02x}{(i * 91) % 256:02x}c0{255 - i * 20:02x}", "out=249",
                                                   "-transition", "composite", "a_track=0", f"b_track={i + 1}",
-                                                  f"geometry={3 + i * 8}%/{5 + i * 7}%:{20 + i}%x{18 + i}%:{50 + i * 5}%"]
+                                                  f"geometry={41 + i * 150}/{30 + i * 80}:{320 + 32 * i}x{180 + 18 * i}:{50 + i * 5}%"]
                                                  for i in range(10)], [])),
     # luma wipe fused with a composite on top (one k_tractor: luma, composite)
     ("luma_then_composite", "yuv422", [100],
@@ -264,21 +266,11 @@ def test_device_frames_stay_resident_through_the_loader_normalisers(tmp_path):
     """melt attaches the loader's rescale/resize/... to every producer; the stock rescale forces yuv422 on
     what it pulls (filter_rescale.c:221-223).  The residency shim (module/filter_rescale.c) must keep the
     device producers' frames in HBM: no upload at all, one download per output frame."""
-    e = mltenv.env(str(tmp_path), cuda=True)
-    e["MLT_CUDA_STATS"] = "1"
     n = 24
-    args = ["noise:", f"out={n - 1}", "-track", "noise:", f"out={n - 1}", "-transition", "composite", "a_track=0", "b_track=1",
-            "geometry=25%/25%:50%x50%:50%", "-track", "colour:0x3060c0a0", f"out={n - 1}", "-transition", "affine", "a_track=0",
+    args = ["noise:", "out=249", "-track", "noise:", "out=249", "-transition", "composite", "a_track=0", "b_track=1",
+            "geometry=25%/25%:50%x50%:50%", "-track", "colour:0x3060c0a0", "out=249", "-transition", "affine", "a_track=0",
             "b_track=2", "rect=10%/10%:50%x50%:90%", "rotate_x=3"]
-    r = subprocess.run([mltenv.MELT, "-profile", "atsc_1080p_25"] + args + ["-consumer", "null", "real_time=-2", "-silent"],
-                       env=e, capture_output=True, text=True, timeout=300)
-    assert r.returncode == 0, r.stderr[-2000:]
-    stats = {}
-    for ln in r.stderr.splitlines():
-        if ln.startswith("[cuda stats]"):
-            name, rest = ln[len("[cuda stats] "):].split("calls")
-            stats[name.strip()] = int(rest.split()[0])
-    assert stats, r.stderr[-2000:]
+    stats, _ = melt_stats(tmp_path, "atsc_1080p_25", args, n)
     frames = stats.get("affine get_image (incl. inputs)")  # one per rendered frame
     assert frames and frames >= n, stats
     assert "upload" not in stats, stats
@@ -317,7 +309,7 @@ def test_cfg4_through_melt_is_one_fused_launch_per_frame(tmp_path):
     k_tractor per frame when the consumer asks for the host image: no k_composite_rows / k_affine launch."""
     n = 24
     stats, err = melt_stats(tmp_path, "uhd_2160p_60", CFG4, n)
-    frames = stats.get("download + sync")
+    frames = stats.get("affine get_image (incl. inputs)")  # one per rendered frame (melt re-renders the last one while it stops)
     assert frames and frames >= n, stats
     assert stats.get("fused pass (k_tractor launches)") == frames, stats
     assert stats.get("ops fused into k_tractor") == 5 * frames, stats
@@ -354,11 +346,12 @@ def test_fused_pass_refusals_fall_back_to_per_op_launches(tmp_path):
     diff = np.abs(ref[3][0].astype(int) - got[3][0].astype(int))
     assert diff.max() <= 2 and (diff > 0).mean() < 1e-4
     stats, _ = melt_stats(tmp_path, prof, CFG4, 8)
+    frames = stats["affine get_image (incl. inputs)"]
     assert "fused pass (k_tractor launches)" not in stats, stats
-    assert stats.get("unfused composite launches") == 2 * stats["download + sync"], stats
-    assert stats.get("unfused affine launches") == stats["download + sync"], stats
+    assert stats.get("unfused composite launches") == 2 * frames, stats
+    assert stats.get("unfused affine launches") == frames, stats
     # (b) rgba64 working format: the affine launches K4, the composites around it stay deferred
-    a64 = ["colour:0x80c04020", "out=249", "-track", "colour:0x3060c0a0", "out=249", "-transition", "affine",
+    a64 = ["abnormal:colour:0x80c04020", "out=249", "-track", "abnormal:colour:0x3060c0a0", "out=249", "-transition", "affine",
            "rect=20%/20%:50%x50%:90%", "rotate_x=0.5", "a_track=0", "b_track=1"]
     ref, _ = dump(tmp_path, "ref64", False, "atsc_1080p_25", "rgba64", [30], a64)
     got, _ = dump(tmp_path, "cuda64", True, "atsc_1080p_25", "rgba64", [30], a64)
@@ -381,6 +374,7 @@ LUMA_FLOAT = [
     ("wipe_rgba64_translucent_over", "rgba64", [f"luma:{mltenv.LUMA_PGM}", "softness=0.2", "alpha_over=1"]),
     ("dissolve_rgba64_translucent_over", "rgba64", ["luma", "alpha_over=1"]),
     ("wipe_yuv422_fix_background", "yuv422", [f"luma:{mltenv.LUMA_PGM}", "softness=0.2", "fix_background_alpha=1"]),
+    ("dissolve_yuv422_fix_background", "yuv422", ["luma", "fix_background_alpha=1"]),
 ]
 
 
@@ -389,8 +383,11 @@ LUMA_FLOAT = [
 def test_translucent_luma_matches_stock_within_1lsb(tmp_path, name, fmt, trans):
     """B = colour:0x3060c0a0 (alpha 0xa0): is_opaque() fails, the reference takes its float paths
     (transition_luma.c:63-129,192-292,417-451,475-723).  The colour tracks are rgba64-native for the rgba64 cases."""
-    a = ["colour:0x80c04020", "out=249"] if fmt == "rgba64" else A
-    args = a + TRANSLUCENT_B + ["-transition"] + trans + ["in=0", "out=249", "a_track=0", "b_track=1"]
+    # rgba64: the loader's rescale normaliser forces yuv422 and this build has no yuv422 -> rgba64 converter
+    # (swscale absent), so the stock services only reach rgba64 through "abnormal:" (loader without normalisers)
+    a = ["abnormal:colour:0x80c04020", "out=249"] if fmt == "rgba64" else A
+    b = ["-track", "abnormal:colour:0x3060c0a0", "out=249"] if fmt == "rgba64" else TRANSLUCENT_B
+    args = a + b + ["-transition"] + trans + ["in=0", "out=249", "a_track=0", "b_track=1"]
     ref, _ = dump(tmp_path, "ref", False, "atsc_1080p_25", fmt, [60, 130], args)
     got, err = dump(tmp_path, "cuda", True, "atsc_1080p_25", fmt, [60, 130], args)
     for f in (60, 130):
