@@ -9,9 +9,13 @@ through mlt_properties inside MLT; this file exists so bench.py and the tests ca
 with exactly the per-frame parameters the reference would use (tests/test_cfg_vs_reference.py
 checks the derivation against frames rendered by the reference itself).
 """
+import ctypes as C
 import math
 
+from . import abi
+
 W_UHD, H_UHD = 3840, 2160
+RGBA, YUV422 = 2, 3
 
 
 def rint(x):
@@ -120,3 +124,67 @@ def shard_frames(rank, world, frames_per_rank, step=0):
     exchange is needed; order is restored by frame index."""
     base = step * world * frames_per_rank + rank * frames_per_rank
     return list(range(base, base + frames_per_rank))
+
+
+# ---- C-ABI descriptors for those parameters (ctypes mirrors of include/mltcuda.h) ---------------------
+
+def geometry_struct(g):
+    return abi.CompositeGeometry(x=g["x"], y=g["y"], w=g["w"], h=g["h"], o=g["o"], nw=g["nw"], nh=g["nh"],
+                                 sw=g["sw"], sh=g["sh"], x_src=g["x_src"], y_src=g["y_src"])
+
+
+def affine_desc(k, a_ptr, b_ptr, W, H, batch=1, a_bs=0, b_bs=0):
+    d = abi.AffineDesc(format=RGBA, a_image=a_ptr, b_image=b_ptr, a_width=W, a_height=H, b_width=k["b_width"],
+                       b_height=k["b_height"], lower_x=k["lower_x"], lower_y=k["lower_y"], dz=k["dz"], mix=k["mix"],
+                       x_offset=k["x_offset"], y_offset=k["y_offset"], minima=k["minima"], xmax=k["xmax"],
+                       ymax=k["ymax"], b_alpha=k["b_alpha"], interp=k["interp"], batch=batch, a_bstride=a_bs,
+                       b_bstride=b_bs)
+    for i in range(3):
+        for j in range(3):
+            d.matrix[i][j] = float(k["matrix"][i][j])
+    return d
+
+
+def composite_desc(ctx, g, dest_ptr, W, H, src_ptr, bw, bh, alpha_a_ptr=None, batch=1, dest_bs=0, src_bs=0, aa_bs=0,
+                   alpha_b_ptr=None, luma_ptr=None, softness=0.0):
+    d = abi.CompositeDesc(batch=batch, dest_bstride=dest_bs, src_bstride=src_bs, alpha_a_bstride=aa_bs)
+    gs = geometry_struct(g)
+    skip = ctx.lib.mltcuda_composite_setup(C.byref(d), dest_ptr, W, H, src_ptr, bw, bh, alpha_b_ptr, alpha_a_ptr, C.byref(gs),
+                                           -1, luma_ptr, softness)
+    assert not skip
+    return d
+
+
+def tractor_desc(ctx, f, in_ptr, out_ptr, out_alpha_ptr, b1_ptr, bc_ptr, b3_ptr, batch=1, bs=None):
+    """The cfg4 op list for mltcuda_tractor.  bs = dict of batch strides."""
+    W, H = f["W"], f["H"]
+    (g1, b1w, b1h), (g2, b2w, b2h), k = f["comp1"], f["comp2"], f["affine"]
+    bs = bs or {}
+    ops = (abi.TractorOp * 5)()
+    ops[0].kind = abi.TOP_COMPOSITE
+    ops[0].u.composite = composite_desc(ctx, g1, out_ptr, W, H, b1_ptr, b1w, b1h, src_bs=bs.get("b1", 0))
+    ops[1].kind, ops[1].to_format = abi.TOP_CONVERT, RGBA
+    ops[2].kind = abi.TOP_AFFINE
+    ops[2].u.affine = affine_desc(k, None, bc_ptr, W, H, b_bs=bs.get("bc", 0))
+    ops[3].kind, ops[3].to_format = abi.TOP_CONVERT, YUV422
+    ops[4].kind = abi.TOP_COMPOSITE
+    ops[4].u.composite = composite_desc(ctx, g2, out_ptr, W, H, b3_ptr, b2w, b2h, src_bs=bs.get("b3", 0))
+    d = abi.TractorDesc(width=W, height=H, in_format=YUV422, out_format=YUV422, in_=in_ptr, out=out_ptr,
+                        out_alpha=out_alpha_ptr, n_ops=5, ops=ops, batch=batch, in_bstride=bs.get("in", 0),
+                        out_bstride=bs.get("out", 0), out_alpha_bstride=bs.get("out_alpha", 0))
+    d._keep = ops
+    return d
+
+
+# ---- cfg1 .. cfg3 (1080p): the single-transition configurations of BASELINE.json ------------------------
+
+CFG1B = dict(name="cfg1b_1080p_composite_blend", geometry=(0.0, 0.0, 1.0, 1.0, 0.5))
+CFG3 = dict(name="cfg3_1080p_affine_rgba", k0=(0, (0.10, 0.10, 0.50, 0.50, 1.0)), k1=(249, (0.30, 0.30, 0.70, 0.70, 0.6)),
+            rotate_x=1.0)
+
+
+def cfg3_frame(position, W=1920, H=1080, cfg=CFG3):
+    (k0, r0), (k1, r1) = cfg["k0"], cfg["k1"]
+    r = lerp_rect(k0, r0, k1, r1, position)
+    rect_px = [r[0] * W, r[1] * H, r[2] * W, r[3] * H, r[4]]
+    return affine_params(W, H, rect_px, position, cfg["rotate_x"], W, H, "bilinear")
