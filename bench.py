@@ -4,35 +4,58 @@ composite + affine + composite with the imageconvert yuv422<->rgba round trip pe
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
-One "step" = FRAMES_PER_STEP consecutive timeline frames of the 4-track graph on one GPU, each
-frame one launch of the fused tractor kernel (mltcuda_tractor) with that frame's own keyframed
-parameters.  `value` = whole-job frames/s with the tracks resident in HBM (CUDA events on the
-launching stream); `e2e` = the same frames through the same C-ABI with HOST (pinned) track buffers:
-per frame H2D of the three noise tracks, the kernel, D2H of the composited frame, double-buffered
-on two streams.  The working set of a step (~1.6 GB) is >> the 126 MB L2, so no L2 flush is needed.
+A "step" = FRAMES_PER_STEP (512) timeline frames of the 4-track graph on one GPU: 32 distinct
+consecutive frames, each with its own keyframed parameters and its own buffers (1.6 GB working set
+>> the 126 MB L2, so no L2 flush), walked 16 times.
+
+ours arm, one JSON line:
+  value     device leg through the C-ABI, per frame: the three device noise producers (k_noise) + ONE
+            fused launch (mltcuda_tractor), round-robin over two worker contexts (= two of MLT's
+            real_time worker threads); CUDA events on the launching stream, max over ranks.
+  roofline  the fused kernel alone (second timed region, same frames): algorithmic bytes per launch
+            / average launch time vs MEASURED_PEAKS.json.
+  e2e       the same graph through the reference-facing plugin: the MLT host `melt` (oracle/_ref/bin,
+            unmodified) with mlt_b200/lib/mlt/libmltcuda.so dropped into its repository, cfg4 command
+            line, -consumer null real_time=-T; every frame is downloaded to (pinned) host memory.
+            Steady state = the difference of a short and a long run of the same process (removes
+            CUDA / MLT start-up, reported beside it).
+  e2e_abi   the round-1 end-to-end leg kept for comparison: pinned host tracks up, kernel, frame down
+            through mltcuda_upload / _tractor / _download.
+  extra     1080p device legs of cfg1 (composite), cfg2 (luma wipe), cfg3 (affine rgba), cfg4.
+  cpu_baseline  the unmodified reference's melt on the host cores (bounded sample).
 N > 1: one process per GPU (torchrun), frames shard by rank, no collective on the data path
 (frames are independent); timing is the max over ranks after a barrier.
 --impl reference: the UNMODIFIED reference (oracle/_ref/bin/melt, built from /root/reference by
-oracle/Makefile.ref) renders the same graph on the host cores with real_time=-nproc.
+oracle/Makefile.ref) renders the same graph on the host cores with real_time=-nproc; a step is a
+bounded 32-frame sample of the 512-frame step, all steps rendered by one melt process, start-up removed
+with a second, shorter run.
 """
 import argparse
 import ctypes as C
 import json
 import os
+import re
 import subprocess
 import sys
+import tempfile
 import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 import numpy as np  # noqa: E402
 
-FRAMES_PER_STEP = 32
+from mlt_b200 import meltenv  # noqa: E402
+
+DISTINCT = 32           # distinct timeline frames resident per GPU
+REPEAT = 16             # walks over them per step
+FRAMES_PER_STEP = DISTINCT * REPEAT
+REF_SAMPLE = 32         # frames of a step the reference arm really renders (bounded sample)
 W, H = 3840, 2160
 METRIC = "composited frames/sec, 4-track uhd_2160p_60 (composite+affine+composite+imageconvert)"
+CONFIG = {"workload": "cfg4_uhd_2160p_60_4track", "width": W, "height": H, "frames_per_step": FRAMES_PER_STEP,
+          "l2": "inputs larger than L2 (32 distinct frames, 1.6 GB working set per GPU)"}
 
 MELT_CFG4 = ["noise:", "out={last}", "-track", "noise:", "out={last}", "-attach", "mirror:flip", "-transition",
              "composite", "a_track=0", "b_track=1", "geometry=5%/5%:40%x40%:80%", "-track", "colour:0x3060c0a0",
@@ -74,68 +97,84 @@ class Dist:
             self.pg.destroy_process_group()
 
 
-# ---- reference arm / CPU baseline ---------------------------------------------------------------
+# ---- melt runs (both arms) ------------------------------------------------------------------------------
 
-def ref_env():
-    ref = os.path.join(ROOT, "oracle", "_ref")
-    e = dict(os.environ)
-    e["MLT_REPOSITORY"] = os.path.join(ref, "lib", "mlt")
-    e["MLT_DATA"] = os.path.join(ref, "share", "mlt")
-    e["MLT_PROFILES_PATH"] = os.path.join(ref, "share", "mlt", "profiles")
-    e["LD_LIBRARY_PATH"] = os.path.join(ref, "lib") + ":" + e.get("LD_LIBRARY_PATH", "")
-    return e, os.path.join(ref, "bin", "melt")
-
-
-def melt_cfg4_seconds(frames, threads):
-    """Wall time of the reference rendering `frames` frames of cfg4 (null consumer never drops)."""
-    env, melt = ref_env()
-    args = [a.format(last=frames - 1) for a in MELT_CFG4]
-    cmd = [melt, "-profile", "uhd_2160p_60"] + args + ["-consumer", "null", f"real_time=-{threads}", "-silent"]
+def melt_seconds(frames, threads, cuda, base, profile="uhd_2160p_60", graph=MELT_CFG4, extra=None):
+    """Wall time of one melt process rendering `frames` frames of the graph into -consumer null
+    (real_time=-threads: frame-parallel workers, never drops).  cuda=False: the stock services of the
+    reference; cuda=True: the same melt with libmltcuda.so in its repository.  Returns (seconds, stderr)."""
+    env = meltenv.env(base, cuda=cuda, extra=extra)
+    args = [a.format(last=frames - 1) for a in graph]
+    cmd = [meltenv.melt_binary(), "-profile", profile] + args + ["-consumer", "null", f"real_time=-{threads}", "-silent"]
     t0 = time.perf_counter()
-    subprocess.run(cmd, env=env, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
-    return time.perf_counter() - t0
+    r = subprocess.run(cmd, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True)
+    dt = time.perf_counter() - t0
+    if r.returncode:
+        raise SystemExit(f"bench.py: melt failed rc={r.returncode}: {r.stderr[-1500:]}")
+    return dt, r.stderr
+
+
+def melt_steady(n_short, n_long, threads, cuda, base, dist=None, **kw):
+    """Two runs of different length: (n_long - n_short) / (t_long - t_short) is the steady-state rate, the
+    rest of the short run is start-up.  With `dist`, every rank runs its own melt (one GPU each), barrier
+    before each run, and the times are the max over ranks."""
+    def one(n):
+        if dist:
+            dist.barrier()
+        t, err = melt_seconds(n, threads, cuda, base, **kw)
+        return (dist.reduce(t, "MAX") if dist else t), err
+    t_short, _ = one(n_short)
+    t_long, err = one(n_long)
+    steady = (n_long - n_short) / max(t_long - t_short, 1e-9)
+    return {"steady_fps": steady, "whole_run_fps": n_long / t_long, "startup_s": max(0.0, t_short - n_short / steady),
+            "t_short": t_short, "t_long": t_long, "n_short": n_short, "n_long": n_long, "stderr": err}
+
+
+def parse_cuda_stats(stderr):
+    """[cuda stats] lines the module prints at exit under MLT_CUDA_STATS=1."""
+    out = {}
+    for ln in stderr.splitlines():
+        m = re.match(r"\[cuda stats\] (.+?)\s+calls\s+(\d+)\s+total\s+([\d.]+) ms\s+mean\s+([\d.]+) us\s+bytes (\d+)", ln)
+        if m:
+            out[m.group(1).strip()] = {"calls": int(m.group(2)), "ms": float(m.group(3)), "bytes": int(m.group(5))}
+    return out
 
 
 def have_reference():
-    return os.path.exists(ref_env()[1])
+    return meltenv.have_mlt()
 
 
-def cpu_port_fps(frames=2):
-    """Fallback CPU baseline: the plain-C oracle chain, 1 thread."""
-    import pipeline
-    inp = pipeline.inputs(0, W, H)
-    t0 = time.perf_counter()
-    for _ in range(frames):
-        pipeline.oracle_chain(inp)
-    return frames / (time.perf_counter() - t0)
+# ---- reference arm ------------------------------------------------------------------------------------------
+
+def reference_fps(steps, warmup, cores, base):
+    """One melt process renders all `steps` samples back to back; a shorter run of `warmup` samples warms the
+    page cache and measures start-up."""
+    n_short = max(1, warmup) * REF_SAMPLE
+    n_long = n_short + steps * REF_SAMPLE
+    return melt_steady(n_short, n_long, cores, False, base)
 
 
 def run_reference(args, dist):
     if dist.rank != 0:
         return
     cores = os.cpu_count() or 1
-    sample_frames = 24
+    base = tempfile.mkdtemp(prefix="mltbench_ref_")
     if have_reference():
         kind = "reference"
-        for _ in range(args.warmup):
-            melt_cfg4_seconds(4, cores)
-        t = 0.0
-        for _ in range(args.steps):
-            t += melt_cfg4_seconds(sample_frames, cores)
-        fps = sample_frames * args.steps / t
-        ms = 1e3 * t / args.steps
-        sample = f"{sample_frames} frames of cfg4 per step through oracle/_ref/bin/melt -consumer null real_time=-{cores}"
+        r = reference_fps(args.steps, args.warmup, cores, base)
+        fps = r["steady_fps"]
+        sample = (f"{REF_SAMPLE} of the {FRAMES_PER_STEP} frames of a step rendered; {args.steps} steps = one "
+                  f"oracle/_ref/bin/melt -consumer null real_time=-{cores} run of {r['n_long']} frames ({r['t_long']:.1f} s) "
+                  f"minus a {r['n_short']}-frame run ({r['t_short']:.1f} s): steady state, start-up {r['startup_s']:.2f} s "
+                  f"excluded; whole-run rate {r['whole_run_fps']:.2f} frames/s; CPU noise producers and mirror:flip included")
+        extra = {"whole_run_fps": round(r["whole_run_fps"], 3), "startup_s": round(r["startup_s"], 3)}
     else:
-        kind, cores = "port", 1
-        t0 = time.perf_counter()
-        fps = cpu_port_fps(max(1, args.steps))
-        ms = 1e3 * (time.perf_counter() - t0) / max(1, args.steps)
-        sample = "1 frame of cfg4 per step through the plain-C oracle chain (oracle/_ref not built)"
+        raise SystemExit("bench.py --impl reference: oracle/_ref is not built (run __graft_entry__.build() where /root/reference exists)")
     line = {"impl": "reference", "metric": METRIC, "value": round(fps, 3), "unit": "frames/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": "cfg4_uhd_2160p_60_4track", "frames_per_step": sample_frames, "width": W, "height": H},
-            "cpu_baseline": {"value": round(fps, 3), "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample},
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * FRAMES_PER_STEP / fps, 3),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": dict(CONFIG),
+            "cpu_baseline": dict({"value": round(fps, 3), "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample}, **extra),
             "e2e": {"value": round(fps, 3), "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -218,11 +257,11 @@ class ClockSampler:
 
 # ---- our arm ---------------------------------------------------------------------------------------
 
-def covered_pixels(aff):
+def covered_pixels(aff, w, h):
     """Destination pixels the affine op touches (dx,dy inside B), counted on a 2x2-subsampled grid."""
     m = aff["matrix"]
-    xs = aff["lower_x"] + np.arange(0, W, 2, dtype=np.float64)
-    ys = aff["lower_y"] + np.arange(0, H, 2, dtype=np.float64)
+    xs = aff["lower_x"] + np.arange(0, w, 2, dtype=np.float64)
+    ys = aff["lower_y"] + np.arange(0, h, 2, dtype=np.float64)
     X, Y = np.meshgrid(xs, ys)
     dx = (m[0][0] * X + m[0][1] * Y + m[0][2]) / aff["dz"] + aff["x_offset"]
     dy = (m[1][0] * X + m[1][1] * Y + m[1][2]) / aff["dz"] + aff["y_offset"]
@@ -230,87 +269,203 @@ def covered_pixels(aff):
     return int(inside.sum()) * 4
 
 
+class Timed:
+    """A timed region on several worker contexts: bracketed by events on workers[0]'s stream; the other
+    workers wait for the start event and workers[0] waits for all of them before the stop event."""
+
+    def __init__(self, lib, workers):
+        self.lib, self.workers = lib, workers
+        self.ev0, self.ev1 = lib.mltcuda_event_create(), lib.mltcuda_event_create()
+        self.joins = [lib.mltcuda_event_create() for _ in workers[1:]]
+
+    def run(self, fn, steps, dist):
+        from mlt_b200 import abi
+        lib, workers = self.lib, self.workers
+        for w in workers:
+            w.sync()
+        dist.barrier()
+        l0 = sum(w.launches() for w in workers)
+        lib.mltcuda_event_record(workers[0].h, self.ev0)
+        for w in workers[1:]:
+            abi.check(lib.mltcuda_ctx_wait_event(w.h, self.ev0), "wait_event")
+        for _ in range(steps):
+            fn()
+        for w, j in zip(workers[1:], self.joins):
+            lib.mltcuda_event_record(w.h, j)
+            abi.check(lib.mltcuda_ctx_wait_event(workers[0].h, j), "wait_event")
+        lib.mltcuda_event_record(workers[0].h, self.ev1)
+        for w in workers:
+            w.sync()
+        dist.barrier()
+        ms = lib.mltcuda_event_elapsed_ms(self.ev0, self.ev1)
+        return ms, sum(w.launches() for w in workers) - l0
+
+
+def cfg4_setup(lib, ctx, first, F, w, h):
+    """Resident tracks + op lists for F consecutive timeline frames of cfg4 at w x h."""
+    from mlt_b200 import abi, workloads
+    frames = [workloads.cfg4_frame(first + i, w, h) for i in range(F)]
+    (g1, b1w, b1h), (g2, b2w, b2h) = frames[0]["comp1"], frames[0]["comp2"]
+    fb, b1b, b3b = w * h * 2, b1w * b1h * 2, b2w * b2h * 2
+    S = dict(frames=frames, fb=fb, b1b=b1b, b3b=b3b, b1=(b1w, b1h), b3=(b2w, b2h), first=first, F=F, w=w, h=h)
+    S["d_in"], S["d_b1"], S["d_b3"] = ctx.alloc(F * fb), ctx.alloc(F * b1b), ctx.alloc(F * b3b)
+    S["d_bc"], d_bcy, d_bca = ctx.alloc(w * h * 4), ctx.alloc(fb), ctx.alloc(w * h)
+    S["d_out"], S["d_alpha"] = ctx.alloc(F * fb), ctx.alloc(F * w * h)
+    # colour B of the affine: the producer's yuv422 + alpha plane converted to rgba, as the normaliser chain does
+    r, g, b, a = workloads.CFG4["colour"]
+    abi.check(lib.mltcuda_colour(ctx.h, d_bcy.ptr, d_bca.ptr, 3, w, h, r, g, b, a), "colour")
+    ctx.call("mltcuda_convert", abi.ConvertDesc(src_format=3, dst_format=2, width=w, height=h, src=d_bcy.ptr,
+                                                dst=S["d_bc"].ptr, src_alpha=d_bca.ptr, batch=1))
+    S["descs"] = [workloads.tractor_desc(ctx, frames[i], S["d_in"].at(i * fb), S["d_out"].at(i * fb), S["d_alpha"].at(i * w * h),
+                                         S["d_b1"].at(i * b1b), S["d_bc"].ptr, S["d_b3"].at(i * b3b)) for i in range(F)]
+    return S
+
+
+def cfg4_steps(lib, S, workers, repeat):
+    """(full step: producers + fused pass per frame, fused pass alone) as closures."""
+    from mlt_b200 import abi
+    F, w, h, fb, b1b, b3b, first = S["F"], S["w"], S["h"], S["fb"], S["b1b"], S["b3b"], S["first"]
+    (b1w, b1h), (b3w, b3h) = S["b1"], S["b3"]
+    nw = len(workers)
+
+    def produce(i, c):
+        # track 0 and track 3: the noise producer at the frame's position; track 1: the same producer re-seeded
+        # (stands in for noise + the CPU filter mirror:flip, which is not part of the path)
+        rc = lib.mltcuda_noise(c.h, S["d_in"].at(i * fb), w, h, first + i, 1, 0)
+        rc |= lib.mltcuda_noise(c.h, S["d_b1"].at(i * b1b), b1w, b1h, first + i + 100000, 1, 0)
+        rc |= lib.mltcuda_noise(c.h, S["d_b3"].at(i * b3b), b3w, b3h, first + i, 1, 0)
+        if rc:
+            abi.check(rc, "mltcuda_noise")
+
+    def full():
+        for _ in range(repeat):
+            for i, d in enumerate(S["descs"]):
+                c = workers[i % nw]
+                produce(i, c)
+                rc = lib.mltcuda_tractor(c.h, C.byref(d))
+                if rc:
+                    abi.check(rc, "mltcuda_tractor")
+
+    def fused_only():
+        for _ in range(repeat):
+            for i, d in enumerate(S["descs"]):
+                rc = lib.mltcuda_tractor(workers[i % nw].h, C.byref(d))
+                if rc:
+                    abi.check(rc, "mltcuda_tractor")
+
+    for i in range(F):
+        produce(i, workers[0])
+    workers[0].sync()
+    return full, fused_only
+
+
+def extra_1080p(lib, ctx, workers, dist, steps):
+    """Device legs of the other BASELINE.json configurations at 1080p (producers inside the timed region)."""
+    from mlt_b200 import abi, workloads
+    w, h, F, rep = 1920, 1080, 64, 4
+    fb = w * h * 2
+    out = {}
+    timed = Timed(lib, workers)
+    nw = len(workers)
+    d_a, d_b = ctx.alloc(F * fb), ctx.alloc(F * fb)
+
+    def produce(i, c):
+        rc = lib.mltcuda_noise(c.h, d_a.at(i * fb), w, h, i, 1, 0) | lib.mltcuda_noise(c.h, d_b.at(i * fb), w, h, i + 100000, 1, 0)
+        if rc:
+            abi.check(rc, "mltcuda_noise")
+
+    def leg(name, per_frame):
+        def step():
+            for _ in range(rep):
+                for i in range(F):
+                    c = workers[i % nw]
+                    produce(i, c)
+                    per_frame(i, c)
+        step()
+        ms, _ = timed.run(step, steps, dist)
+        out[name] = round(dist.world * F * rep * steps / (dist.reduce(ms, "MAX") / 1e3), 1)
+
+    # cfg1: composite, full frame, 50 % (SSE2 case 1)
+    g, bw, bh = workloads.composite_geometry(workloads.CFG1B["geometry"], w, h, w, h)
+    c1 = [workloads.composite_desc(ctx, g, d_a.at(i * fb), w, h, d_b.at(i * fb), bw, bh) for i in range(F)]
+    leg("cfg1_composite_1080p", lambda i, c: abi.check(lib.mltcuda_composite(c.h, C.byref(c1[i])), "composite"))
+    # cfg2: luma wipe, softness 0.2, 720x576 map (a ramp with the dynamic range of demo/luma1.pgm)
+    lw, lh = 720, 576
+    ramp = (np.arange(lw * lh, dtype=np.uint32) % lw * 65535 // (lw - 1)).astype(np.uint16)
+    d_map = ctx.put(ramp)
+    c2 = [abi.LumaDesc(format=3, dest=d_a.at(i * fb), src=d_b.at(i * fb), map=d_map.ptr, luma_width=lw, luma_height=lh,
+                       width=w, height=h, width_dest=w, height_dest=h, width_src=w, height_src=h, pos=(i + 0.5) / F,
+                       frame_delta=1.0 / 250, softness=0.2, field_order=-1, translucent=0, batch=1) for i in range(F)]
+    leg("cfg2_luma_wipe_1080p", lambda i, c: abi.check(lib.mltcuda_luma(c.h, C.byref(c2[i])), "luma"))
+    # cfg3: affine over rgba tracks: A -> rgba and the transform fused, B -> rgba on its own (as the reference converts it)
+    d_brgba, d_out = ctx.alloc(F * fb * 2), ctx.alloc(F * fb * 2)
+    k = [workloads.cfg3_frame(i * 249 // F, w, h) for i in range(F)]
+    cv = [abi.ConvertDesc(src_format=3, dst_format=2, width=w, height=h, src=d_b.at(i * fb), dst=d_brgba.at(i * fb * 2), batch=1)
+          for i in range(F)]
+    t3 = []
+    for i in range(F):
+        ops = (abi.TractorOp * 2)()
+        ops[0].kind, ops[0].to_format = abi.TOP_CONVERT, 2
+        ops[1].kind = abi.TOP_AFFINE
+        ops[1].u.affine = workloads.affine_desc(k[i], None, d_brgba.at(i * fb * 2), w, h)
+        d = abi.TractorDesc(width=w, height=h, in_format=3, out_format=2, in_=d_a.at(i * fb), out=d_out.at(i * fb * 2), n_ops=2,
+                            ops=ops, batch=1)
+        d._keep = ops
+        t3.append(d)
+
+    def cfg3(i, c):
+        rc = lib.mltcuda_convert(c.h, C.byref(cv[i])) or lib.mltcuda_tractor(c.h, C.byref(t3[i]))
+        if rc:
+            abi.check(rc, "cfg3")
+    leg("cfg3_affine_rgba_1080p", cfg3)
+    # cfg4 at 1080p
+    S = cfg4_setup(lib, ctx, 0, F, w, h)
+    full, _ = cfg4_steps(lib, S, workers, rep)
+    full()
+    ms, _ = timed.run(full, steps, dist)
+    out["cfg4_4track_1080p"] = round(dist.world * F * rep * steps / (dist.reduce(ms, "MAX") / 1e3), 1)
+    return out
+
+
 def run_ours(args, dist):
-    import pipeline
     from mlt_b200 import Context, abi, workloads
     lib = abi.load()
     ndev = lib.mltcuda_device_count()
     if ndev <= 0:
         raise SystemExit("bench.py: no CUDA device visible; the product path has no CPU fallback")
     dev = dist.local_rank % ndev
-    ctx = Context(dev)
-    ctx2 = Context(dev)  # second stream for the double-buffered end-to-end leg
-    F = FRAMES_PER_STEP
+    # Consecutive frames go round-robin to the worker contexts of this GPU, as MLT's real_time=-N worker
+    # threads do (one context = one worker = one stream, DESIGN 2): the tail wave of one frame's launch
+    # overlaps the head of the next frame's.
+    workers = [Context(dev) for _ in range(max(1, min(8, args.streams)))]
+    ctx = workers[0]
+    F = DISTINCT
     first = workloads.shard_frames(dist.rank, dist.world, F)[0]  # each rank renders its own slice of the timeline
-    frames = [workloads.cfg4_frame(first + i, W, H) for i in range(F)]
-    (g1, b1w, b1h), (g2, b2w, b2h) = frames[0]["comp1"], frames[0]["comp2"]
-    fb, b1b, b3b = W * H * 2, b1w * b1h * 2, b2w * b2h * 2
+    S = cfg4_setup(lib, ctx, first, F, W, H)
+    fb, b1b, b3b, frames = S["fb"], S["b1b"], S["b3b"], S["frames"]
+    full, fused_only = cfg4_steps(lib, S, workers, REPEAT)
+    timed = Timed(lib, workers)
 
-    # resident tracks: device-side noise producers (bit-exact with producer_noise.c), flipped track 1
-    # uploaded from the oracle-free host path below
-    d_in, d_b1, d_b3 = ctx.alloc(F * fb), ctx.alloc(F * b1b), ctx.alloc(F * b3b)
-    d_bc, d_bcy, d_bca = ctx.alloc(W * H * 4), ctx.alloc(fb), ctx.alloc(W * H)
-    d_out, d_alpha = ctx.alloc(F * fb), ctx.alloc(F * W * H)
-    abi.check(lib.mltcuda_noise(ctx.h, d_in.ptr, W, H, first, F, fb), "noise")
-    abi.check(lib.mltcuda_noise(ctx.h, d_b3.ptr, b2w, b2h, first, F, b3b), "noise")
-    abi.check(lib.mltcuda_noise(ctx.h, d_b1.ptr, b1w, b1h, first + 100000, F, b1b), "noise")  # decorrelated track 1
-    r, g, b, a = workloads.CFG4["colour"]
-    abi.check(lib.mltcuda_colour(ctx.h, d_bcy.ptr, d_bca.ptr, 3, W, H, r, g, b, a), "colour")
-    ctx.call("mltcuda_convert", abi.ConvertDesc(src_format=3, dst_format=2, width=W, height=H, src=d_bcy.ptr,
-                                                dst=d_bc.ptr, src_alpha=d_bca.ptr, batch=1))
-    ctx.sync()
-
-    descs = [pipeline.tractor_desc(ctx, frames[i], d_in.at(i * fb), d_out.at(i * fb), d_alpha.at(i * W * H),
-                                   d_b1.at(i * b1b), d_bc.ptr, d_b3.at(i * b3b)) for i in range(F)]
-
-    # Consecutive frames go round-robin to STREAMS contexts of this GPU, as MLT's real_time=-N worker
-    # threads do (one context = one worker = one stream): the tail wave of one frame's
-    # launch overlaps the head of the next frame's.  The timed region is bracketed on workers[0]'s
-    # stream: every other worker waits for the start event, and workers[0] waits for all of them
-    # before the stop event is recorded.
-    workers = [ctx, ctx2] + [Context(dev) for _ in range(max(0, min(8, args.streams) - 2))]
-    workers = workers[:max(1, args.streams)]
-
-    def step():
-        for i, d in enumerate(descs):
-            rc = lib.mltcuda_tractor(workers[i % len(workers)].h, C.byref(d))
-            if rc:
-                abi.check(rc, "mltcuda_tractor")
-
-    ev0, ev1 = lib.mltcuda_event_create(), lib.mltcuda_event_create()
-    joins = [lib.mltcuda_event_create() for _ in workers[1:]]
-    for _ in range(args.warmup):
-        step()
-    for w in workers:
-        w.sync()
+    # ---- device leg: producers + fused pass --------------------------------------------------------
+    for _ in range(max(1, args.warmup // 2)):
+        full()
     clocks = ClockSampler(dev)
     clocks.start()
-    dist.barrier()
-    l0 = sum(w.launches() for w in workers)
-    lib.mltcuda_event_record(ctx.h, ev0)
-    for w in workers[1:]:
-        abi.check(lib.mltcuda_ctx_wait_event(w.h, ev0), "wait_event")
-    for _ in range(args.steps):
-        step()
-    for w, j in zip(workers[1:], joins):
-        lib.mltcuda_event_record(w.h, j)
-        abi.check(lib.mltcuda_ctx_wait_event(ctx.h, j), "wait_event")
-    lib.mltcuda_event_record(ctx.h, ev1)
-    for w in workers:
-        w.sync()
-    dist.barrier()
-    ms = lib.mltcuda_event_elapsed_ms(ev0, ev1)
-    launches = sum(w.launches() for w in workers) - l0
+    ms, launches = timed.run(full, args.steps, dist)
+    # ---- the fused kernel alone (roofline) -----------------------------------------------------------
+    fused_only()
+    ms_k, launches_k = timed.run(fused_only, args.steps, dist)
     clk = clocks.stop()
     ms_max = dist.reduce(ms, "MAX")
     total_launches = int(dist.reduce(launches, "SUM"))
-    value = dist.world * F * args.steps / (ms_max / 1e3)
+    value = dist.world * FRAMES_PER_STEP * args.steps / (ms_max / 1e3)
+    value_k = dist.world * FRAMES_PER_STEP * args.steps / (dist.reduce(ms_k, "MAX") / 1e3)
 
-    # roofline of the dominant (only) kernel: algorithmic bytes per launch / average launch time
-    cov = [covered_pixels(f["affine"]) for f in frames]
+    # roofline of the dominant kernel: algorithmic bytes per launch / average launch time
+    cov = [covered_pixels(f["affine"], W, H) for f in frames]
     alg = [W * H * (2 + 2 + 1) + b1b + b3b + 4 * c for c in cov]  # A r2 + out w2 + alpha w1, layers once, 4 B/covered px
     alg_per_launch = float(np.mean(alg))
-    avg_launch_s = (ms / 1e3) / max(launches, 1)
+    avg_launch_s = (ms_k / 1e3) / max(launches_k, 1)
     achieved = alg_per_launch / avg_launch_s / 1e9
     peaks = {}
     try:
@@ -318,26 +473,93 @@ def run_ours(args, dist):
     except OSError:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    traffic = None  # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed ncu --set full capture
+    traffic = dram_read = None  # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed ncu --set full capture
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "k_tractor_traffic.json")))["dram_bytes_per_launch"]
+        tj = json.load(open(os.path.join(ROOT, "profiles", "k_tractor_traffic.json")))
+        traffic, dram_read = tj["dram_bytes_per_launch"], tj.get("dram_read_bytes")
     except (OSError, KeyError, ValueError):
         pass
     # measured DRAM reads (ncu) + the bytes the kernel stores (most of a launch's stores are still in
     # the 126 MB L2 when it ends, so ncu's write counter under-counts them): what HBM really moves
-    dram_est = None
-    try:
-        dram_est = json.load(open(os.path.join(ROOT, "profiles", "k_tractor_traffic.json")))["dram_read_bytes"] + W * H * 3
-    except (OSError, KeyError, ValueError):
-        pass
+    dram_est = dram_read + W * H * 3 if dram_read else None
     roofline = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(achieved / peak, 4), "traffic": traffic, "kernel": "k_tractor",
+                "kernel_only_fps": round(value_k, 1), "avg_launch_us": round(avg_launch_s * 1e6, 2),
                 "dram_gbs_est": round(dram_est / avg_launch_s / 1e9, 1) if dram_est else None,
                 "dram_frac_est": round(dram_est / avg_launch_s / 1e9 / peak, 4) if dram_est else None,
                 "algorithmic_bytes_per_launch": int(alg_per_launch),
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s"}
 
-    # ---- end to end: host (pinned) tracks in, composited frame out, two streams -------------------
+    extra = extra_1080p(lib, ctx, workers, dist, max(2, min(5, args.steps))) if not args.no_extra else None
+
+    # ---- end to end through the C-ABI: host (pinned) tracks in, composited frame out ------------------
+    e2e_abi = None
+    if not args.no_e2e_abi:
+        e2e_abi = e2e_abi_leg(lib, dist, workers, S, max(1, min(args.steps, 5)), dev)
+
+    # ---- end to end through the plugin: melt + libmltcuda.so ------------------------------------------
+    for w_ in workers:
+        w_.sync()
+    e2e = None
+    threads = args.melt_threads or max(2, min(8, (os.cpu_count() or 8) // max(1, dist.world)))
+    if have_reference() and meltenv.have_module():
+        base = tempfile.mkdtemp(prefix=f"mltbench_{dist.rank}_")
+        ex = {"MLT_CUDA_DEVICE": str(dev), "MLT_CUDA_STATS": "1"}
+        r = melt_steady(args.melt_short, args.melt_short + args.melt_frames, threads, True, base, dist=dist, extra=ex)
+        st = parse_cuda_stats(r["stderr"])
+        rendered = max(1, st.get("affine get_image (incl. inputs)", {}).get("calls", r["n_long"]))
+        h2d = st.get("upload", {}).get("bytes", 0) / rendered
+        d2h = st.get("download + sync", {}).get("bytes", 0) / rendered
+        e2e = {"value": round(dist.world * r["steady_fps"], 1), "unit": "frames/s",
+               "h2d_bytes_per_step": int(dist.world * h2d * FRAMES_PER_STEP), "d2h_bytes_per_step": int(dist.world * d2h * FRAMES_PER_STEP),
+               "path": f"oracle/_ref/bin/melt (unmodified MLT host) + mlt_b200/lib/mlt/libmltcuda.so, cfg4 command line, -consumer null "
+                       f"real_time=-{threads}, one melt per GPU",
+               "how": f"steady state: ({r['n_long']} - {r['n_short']}) frames / ({r['t_long']:.2f} - {r['t_short']:.2f}) s, max over ranks",
+               "whole_run_fps": round(dist.world * r["whole_run_fps"], 1), "startup_s": round(r["startup_s"], 2),
+               "fused_launches_per_frame": round(st.get("fused pass (k_tractor launches)", {}).get("calls", 0) / rendered, 3),
+               "unfused_compositing_launches": sum(st.get(k, {}).get("calls", 0) for k in
+                                                   ("unfused composite launches", "unfused affine launches", "unfused luma launches")),
+               "h2d_bytes_per_frame": int(h2d), "d2h_bytes_per_frame": int(d2h)}
+    elif e2e_abi:
+        e2e = dict(e2e_abi, path="C-ABI only (no MLT install to host the module)")
+
+    cpu = None
+    if dist.rank == 0 and dist.world == 1 and not args.no_cpu_baseline and have_reference():
+        cores = os.cpu_count() or 1
+        r = melt_steady(2 * REF_SAMPLE, 2 * REF_SAMPLE + 12 * REF_SAMPLE, cores, False, tempfile.mkdtemp(prefix="mltbench_cpu_"))
+        cpu = {"value": round(r["steady_fps"], 3), "unit": "frames/s", "cores": cores, "kind": "reference",
+               "whole_run_fps": round(r["whole_run_fps"], 3), "startup_s": round(r["startup_s"], 3),
+               "sample": f"{r['n_long'] - r['n_short']} frames of cfg4, steady state of oracle/_ref/bin/melt -consumer null "
+                         f"real_time=-{cores} ({r['n_long']}-frame run {r['t_long']:.1f} s minus {r['n_short']}-frame run "
+                         f"{r['t_short']:.1f} s), CPU noise producers and mirror:flip included"}
+
+    if dist.rank == 0:
+        line = {"metric": METRIC, "value": round(value, 1), "unit": "frames/s", "n_gpus": dist.world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_max / args.steps, 4),
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": dict(CONFIG),
+                "arm": {"timed_region": "per frame 3 k_noise (tracks 0, 1, 3) + 1 k_tractor; track 1 = re-seeded device noise "
+                                        "(the CPU filter mirror:flip of the melt graph is not on the path and is excluded); "
+                                        "colour track resident (constant)",
+                        "launches_per_frame": round(total_launches / (dist.world * FRAMES_PER_STEP * args.steps), 3),
+                        "worker_streams": len(workers), "parallelism": f"frame-sharded x{dist.world}, no collective"},
+                "e2e": e2e, "gpu_launches": total_launches, "roofline": roofline, "clocks": clk}
+        if e2e_abi:
+            line["e2e_abi"] = e2e_abi
+        if extra:
+            line["extra"] = extra
+        if cpu:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    for w_ in workers:
+        w_.close()
+
+
+def e2e_abi_leg(lib, dist, workers, S, steps, dev):
+    from mlt_b200 import Context, abi, workloads
+    F, fb, b1b, b3b, frames = S["F"], S["fb"], S["b1b"], S["b3b"], S["frames"]
+    ctx = workers[0]
+
     def pinned(nbytes):
         p = lib.mltcuda_host_alloc(nbytes)
         if not p:
@@ -346,9 +568,9 @@ def run_ours(args, dist):
 
     NS = max(2, min(8, int(os.environ.get("MLTCUDA_E2E_SLOTS", "2"))))  # frames in flight: one worker context each
     h_in, h_b1, h_b3, h_out = pinned(F * fb), pinned(F * b1b), pinned(F * b3b), pinned(NS * fb)
-    abi.check(lib.mltcuda_download(ctx.h, h_in, d_in.ptr, F * fb))
-    abi.check(lib.mltcuda_download(ctx.h, h_b1, d_b1.ptr, F * b1b))
-    abi.check(lib.mltcuda_download(ctx.h, h_b3, d_b3.ptr, F * b3b))
+    abi.check(lib.mltcuda_download(ctx.h, h_in, S["d_in"].ptr, F * fb))
+    abi.check(lib.mltcuda_download(ctx.h, h_b1, S["d_b1"].ptr, F * b1b))
+    abi.check(lib.mltcuda_download(ctx.h, h_b3, S["d_b3"].ptr, F * b3b))
     ctx.sync()
     slots = []
     e2e_ctxs = (workers + [Context(dev) for _ in range(NS)])[:NS]
@@ -356,8 +578,8 @@ def run_ours(args, dist):
         sl = dict(ctx=c, d_in=c.alloc(fb), d_b1=c.alloc(b1b), d_b3=c.alloc(b3b), d_out=c.alloc(fb), d_al=c.alloc(W * H),
                   done=lib.mltcuda_event_create(), used=False, h_out=h_out + s * fb)
         slots.append(sl)
-    e2e_descs = [[pipeline.tractor_desc(sl["ctx"], frames[i], sl["d_in"].ptr, sl["d_out"].ptr, sl["d_al"].ptr,
-                                        sl["d_b1"].ptr, d_bc.ptr, sl["d_b3"].ptr) for i in range(F)] for sl in slots]
+    e2e_descs = [[workloads.tractor_desc(sl["ctx"], frames[i], sl["d_in"].ptr, sl["d_out"].ptr, sl["d_al"].ptr,
+                                         sl["d_b1"].ptr, S["d_bc"].ptr, sl["d_b3"].ptr) for i in range(F)] for sl in slots]
 
     def e2e_step():
         for i in range(F):
@@ -376,57 +598,27 @@ def run_ours(args, dist):
             lib.mltcuda_event_record(c.h, sl["done"])
             sl["used"] = True
 
-    e2e_steps = max(1, min(args.steps, 5))
     e2e_step()
     for c in e2e_ctxs:
         c.sync()
     dist.barrier()
     t0 = time.perf_counter()
-    for _ in range(e2e_steps):
+    for _ in range(steps):
         e2e_step()
     for c in e2e_ctxs:
         c.sync()
     e2e_s = time.perf_counter() - t0
     dist.barrier()
     e2e_max = dist.reduce(e2e_s, "MAX")
-    e2e_val = dist.world * F * e2e_steps / e2e_max
     # the end-to-end result is the frame the device-resident leg produced
     out_host = np.ctypeslib.as_array(C.cast(h_out, C.POINTER(C.c_uint8)), shape=(NS, fb))
-    ref_out = ctx.get(d_out, (fb,), offset=(F - 1) * fb)
-    e2e_ok = bool(np.array_equal(out_host[(F - 1) % NS], ref_out))
-
-    cpu = None
-    if dist.rank == 0 and dist.world == 1 and not args.no_cpu_baseline:
-        cores = os.cpu_count() or 1
-        if have_reference():
-            melt_cfg4_seconds(4, cores)
-            n = 48
-            t = melt_cfg4_seconds(n, cores)
-            cpu = {"value": round(n / t, 3), "unit": "frames/s", "cores": cores, "kind": "reference",
-                   "sample": f"{n} frames of cfg4 through oracle/_ref/bin/melt -consumer null real_time=-{cores} "
-                             f"({t:.1f} s wall, incl. the CPU noise producers)"}
-        else:
-            cpu = {"value": round(cpu_port_fps(2), 3), "unit": "frames/s", "cores": 1, "kind": "port",
-                   "sample": "2 frames of cfg4 through the plain-C oracle chain"}
-
-    if dist.rank == 0:
-        line = {"metric": METRIC, "value": round(value, 1), "unit": "frames/s", "n_gpus": dist.world,
-                "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_max / args.steps, 4),
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-                "config": {"workload": "cfg4_uhd_2160p_60_4track", "frames_per_step": F, "width": W, "height": H,
-                           "launches_per_frame": 1, "worker_streams": len(workers), "l2": "inputs larger than L2 (step working set ~1.6 GB)",
-                           "parallelism": f"frame-sharded x{dist.world}, no collective"},
-                "e2e": {"value": round(e2e_val, 1), "unit": "frames/s", "h2d_bytes_per_step": dist.world * F * (fb + b1b + b3b),
-                        "d2h_bytes_per_step": dist.world * F * fb, "steps": e2e_steps, "matches_device_leg": e2e_ok,
-                        "h2d_gbs": round(F * (fb + b1b + b3b) * e2e_steps / e2e_s / 1e9, 1),
-                        "d2h_gbs": round(F * fb * e2e_steps / e2e_s / 1e9, 1),
-                        "bound": "PCIe host->device (same rate with 2, 3, 4 or 8 frames in flight)"},
-                "gpu_launches": total_launches, "roofline": roofline, "clocks": clk}
-        if cpu:
-            line["cpu_baseline"] = cpu
-        print(json.dumps(line), flush=True)
-    ctx2.close()
-    ctx.close()
+    ref_out = ctx.get(S["d_out"], (fb,), offset=(F - 1) * fb)
+    ok = bool(np.array_equal(out_host[(F - 1) % NS], ref_out))
+    return {"value": round(dist.world * F * steps / e2e_max, 1), "unit": "frames/s",
+            "h2d_bytes_per_step": dist.world * FRAMES_PER_STEP * (fb + b1b + b3b), "d2h_bytes_per_step": dist.world * FRAMES_PER_STEP * fb,
+            "frames": F * steps, "matches_device_leg": ok, "h2d_gbs": round(F * (fb + b1b + b3b) * steps / e2e_s / 1e9, 1),
+            "d2h_gbs": round(F * fb * steps / e2e_s / 1e9, 1),
+            "path": "mltcuda_upload x3 (pinned noise tracks) + mltcuda_tractor + mltcuda_download per frame, 2 frames in flight"}
 
 
 def main():
@@ -436,7 +628,12 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the 1080p cfg1..cfg4 device legs")
+    ap.add_argument("--no-e2e-abi", action="store_true", help="skip the C-ABI-only end-to-end leg")
     ap.add_argument("--streams", type=int, default=2, help="worker contexts (streams) per GPU on the device leg, 1..8")
+    ap.add_argument("--melt-threads", type=int, default=0, help="real_time=-T of the melt + module leg (0 = auto)")
+    ap.add_argument("--melt-short", type=int, default=64, help="frames of the short (start-up) melt run")
+    ap.add_argument("--melt-frames", type=int, default=6000, help="frames the long melt run adds to the short one")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     dist = Dist()
