@@ -151,6 +151,11 @@ MLT_REPOSITORY
         MLT_REGISTER(mlt_service_filter_type, "imageconvert", create_filter);
         MLT_REGISTER_METADATA(mlt_service_filter_type, "imageconvert", metadata, yml[3]);
     }
+    /* link flavour, as the reference registers it (core/factory.c:248): mlt_link_filter_init wraps the
+     * filter of the same name, which the lines above resolve to this module */
+    MLT_REGISTER(mlt_service_link_type, "cuda.imageconvert", mlt_link_filter_init);
+    if (override_enabled())
+        MLT_REGISTER(mlt_service_link_type, "imageconvert", mlt_link_filter_init);
     MLT_REGISTER(mlt_service_producer_type, "cuda.colour", create_producer);
     MLT_REGISTER_METADATA(mlt_service_producer_type, "cuda.colour", metadata, "producer_colour.yml");
     MLT_REGISTER(mlt_service_producer_type, "cuda.noise", create_producer);

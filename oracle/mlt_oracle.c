@@ -6,10 +6,13 @@
  * load this.  The product (mlt_b200/) never links or calls it.
  *
  * Parity pin: checked against the UNMODIFIED reference compiled into oracle/_ref (Makefile.ref)
- * by tests/test_oracle_vs_ref.py (live, when oracle/_ref exists) and against the committed
- * fixtures tests/golden/ (npz files) that oracle/gen_golden.py produced by calling that build
- * (composite_line_yuv, interp*_b32/_b64 via dlopen; imageconvert / luma / affine / composite
- * frames via the public MLT API).  The reference's own test-suite holds no vectors for this path
+ * by tests/test_oracle_pinning.py and tests/test_cfg_vs_reference.py (live, when oracle/_ref
+ * exists) and against the committed fixtures tests/golden/ (npz files, frames.json) that
+ * tests/golden/make_golden.py produced by calling that build (composite_line_yuv,
+ * interp*_b32/_b64 via dlopen; imageconvert / luma / affine / composite frames via the public MLT
+ * API, oracle/mlt_dump.c).  The float luma paths (translucent wipes and dissolves, rgba64) are
+ * pinned where they run: tests/test_module.py renders them with the stock services and with the
+ * CUDA services inside the reference's own melt (+-1 LSB).  The reference's own test-suite holds no vectors for this path
  * (SURVEY.md 4, 8c).  rgba64 colour conversion is defined by this project ("parity unpinned":
  * libswscale, not in the reference tree).
  *
