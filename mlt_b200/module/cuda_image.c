@@ -185,6 +185,8 @@ void cuda_image_close(cuda_image ci)
         mltcuda_free(ci->ctx, ci->data);
     if (ci->alpha)
         mltcuda_free(ci->ctx, ci->alpha);
+    if (ci->ready)
+        mltcuda_event_destroy(ci->ready);
     ci->magic = 0;
     free(ci);
 }
@@ -279,6 +281,22 @@ int cuda_image_localize(cuda_image b, mltcuda_ctx *ctx)
     mltcuda_free(b->ctx, b->alpha);
     b->data = data, b->alpha = alpha, b->ctx = ctx;
     return 0;
+}
+
+int cuda_image_mark_ready(cuda_image a)
+{
+    if (cuda_image_flush(a))
+        return 1;
+    if (!a->ready && !(a->ready = mltcuda_event_create()))
+        return 1;
+    return mltcuda_event_record(a->ctx, a->ready);
+}
+
+int cuda_image_wait_ready(cuda_image a)
+{
+    if (!a->ready)
+        return cuda_image_flush(a) || mltcuda_ctx_sync(a->ctx);
+    return mltcuda_event_sync(a->ready);
 }
 
 void cuda_image_used_by(cuda_image b, mltcuda_ctx *ctx)
@@ -634,6 +652,10 @@ static int convert_image_impl(mlt_frame frame, uint8_t **image, mlt_image_format
         return 1; /* another module's request */
     if (ci && resident)
         return 0; /* stays in HBM; the asking service converts on the device if it must */
+    /* a device consumer (consumer_null.c) asked for mlt_image_private and one of our services
+     * answered: the picture stays in HBM, its deferred list has run (cuda_consumer_handoff) */
+    if (ci && output == mlt_image_private && mlt_properties_get_int(p, "consumer." CUDA_CONSUMER) > 0)
+        return 0;
 
     if (!ci) { /* host image */
         /* host -> host is the imageconvert filter's job, in the filter's place in the chain (the
@@ -702,6 +724,17 @@ static int cuda_imageconvert_image(mlt_frame frame, uint8_t **image, mlt_image_f
 void cuda_imageconvert_attach(mlt_frame frame)
 {
     mlt_frame_append_convert_image(frame, cuda_imageconvert_image);
+}
+
+/* Called by the CUDA transitions right before they return their image: when nobody of this module is
+ * pulling (the request comes from outside) and the consumer declared that it takes device frames,
+ * this is the hand-off -- the deferred list runs now and the event the consumer waits on is recorded. */
+int cuda_consumer_handoff(mlt_frame frame, cuda_image ci)
+{
+    mlt_properties p = MLT_FRAME_PROPERTIES(frame);
+    if (mlt_properties_get_int(p, CUDA_REQUESTED) > 0 || mlt_properties_get_int(p, "consumer." CUDA_CONSUMER) <= 0)
+        return 0;
+    return cuda_image_mark_ready(ci);
 }
 
 /* ---- pulling inputs ------------------------------------------------------------------------------------ */

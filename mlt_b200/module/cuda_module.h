@@ -28,6 +28,7 @@
 #define CUDA_IMAGE_TAG "mlt_image_private"
 #define CUDA_IMAGE_TAG_VALUE "cuda"
 #define CUDA_REQUESTED "_cuda_requested"
+#define CUDA_CONSUMER "_cuda_consumer" /* the consumer itself takes device frames (consumer_null.c): flush at hand-off, no download */
 #define CUDA_WORK_FORMAT "_cuda_work_format" /* format the pulling service will work in (hint for device producers) */
 
 /* Deferred op list of one image (precedent: the per-frame effect chain of
@@ -55,6 +56,7 @@ struct cuda_image_s
     void *data;            /* device; with pending ops: the bottom track in pending->base_format */
     uint8_t *alpha;        /* device, 1 B/px, or NULL (same remark) */
     cuda_pending *pending; /* NULL = the buffers hold the image */
+    mltcuda_event *ready;  /* recorded behind the last launch when the image is handed to a device consumer */
 };
 
 /* --- runtime (cuda_image.c) -------------------------------------------------------------- */
@@ -103,6 +105,10 @@ int cuda_image_can_defer(cuda_image a);
 int cuda_image_defer(cuda_image a, const mltcuda_tractor_op *op, cuda_image keep);
 /* Run a's pending ops (one fused launch) so that data / alpha hold the image.  0 on success. */
 int cuda_image_flush(cuda_image a);
+/* Device-consumer hand-off: run the pending ops and record `ready` behind them / wait for it. */
+int cuda_image_mark_ready(cuda_image a);
+int cuda_image_wait_ready(cuda_image a);
+int cuda_consumer_handoff(mlt_frame frame, cuda_image ci); /* see cuda_image.c */
 /* Will the image have an alpha plane once its pending ops have run? */
 int cuda_image_has_alpha(cuda_image a);
 /* Make `b` (materialised) readable by kernels launched on `ctx`: same context -> nothing; same GPU,
@@ -159,5 +165,6 @@ mlt_transition cuda_transition_composite_init(mlt_profile, mlt_service_type, con
 mlt_transition cuda_transition_luma_init(mlt_profile, mlt_service_type, const char *, char *);
 mlt_transition cuda_transition_affine_init(mlt_profile, mlt_service_type, const char *, char *);
 mlt_filter cuda_filter_imageconvert_init(mlt_profile, mlt_service_type, const char *, char *);
+mlt_consumer cuda_consumer_null_init(mlt_profile, mlt_service_type, const char *, char *);
 
 #endif

@@ -54,6 +54,11 @@ static void *create_producer(mlt_profile profile, mlt_service_type type, const c
     return NULL;
 }
 
+static void *create_consumer(mlt_profile profile, mlt_service_type type, const char *id, const void *arg)
+{
+    return cuda_consumer_null_init(profile, type, id, (char *) arg);
+}
+
 static int override_enabled(void)
 {
     const char *e = getenv("MLT_CUDA_OVERRIDE");
@@ -156,6 +161,8 @@ MLT_REPOSITORY
     MLT_REGISTER(mlt_service_link_type, "cuda.imageconvert", mlt_link_filter_init);
     if (override_enabled())
         MLT_REGISTER(mlt_service_link_type, "imageconvert", mlt_link_filter_init);
+    MLT_REGISTER(mlt_service_consumer_type, "cuda.null", create_consumer);
+    MLT_REGISTER_METADATA(mlt_service_consumer_type, "cuda.null", metadata, "consumer_null.yml");
     MLT_REGISTER(mlt_service_producer_type, "cuda.colour", create_producer);
     MLT_REGISTER_METADATA(mlt_service_producer_type, "cuda.colour", metadata, "producer_colour.yml");
     MLT_REGISTER(mlt_service_producer_type, "cuda.noise", create_producer);

@@ -432,3 +432,25 @@ def test_affine_properties_match_stock(tmp_path, name, props):
         d = np.abs(ref[f][0].astype(int) - got[f][0].astype(int))
         print(f"{name} frame {f}: {int((d > 0).sum())} of {d.size} differ, max {int(d.max())}")
         assert d.max() <= 1 and (d > 0).mean() < 1e-4
+
+
+@pytest.mark.gpu
+def test_cuda_null_consumer_takes_device_frames(tmp_path):
+    """-consumer cuda.null asks for mlt_image_private; frames stay in HBM (no download), the
+    deferred list still runs once per frame."""
+    e = mltenv.env(str(tmp_path), cuda=True)
+    e["MLT_CUDA_STATS"] = "1"
+    n = 24
+    args = [a.replace("out=249", f"out={n - 1}").replace("out=599", f"out={n - 1}") for a in CFG4 if a != "mirror:flip" and a != "-attach"]
+    r = subprocess.run([mltenv.MELT, "-profile", "uhd_2160p_60"] + args + ["-consumer", "cuda.null", "real_time=-2", "terminate_on_pause=1",
+                                                                            "-silent"], env=e, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    stats = {}
+    for ln in r.stderr.splitlines():
+        if ln.startswith("[cuda stats]") and "calls" in ln:
+            name, rest = ln[len("[cuda stats] "):].split("calls")
+            stats[name.strip()] = int(rest.split()[0])
+    frames = stats.get("affine get_image (incl. inputs)")
+    assert frames and frames >= n, (stats, r.stderr[-1500:])
+    assert "download + sync" not in stats and "upload" not in stats, stats
+    assert stats.get("fused pass (k_tractor launches)") == frames, stats
