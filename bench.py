@@ -17,8 +17,9 @@ ours arm, one JSON line:
   e2e       the same graph through the reference-facing plugin: the MLT host `melt` (oracle/_ref/bin,
             unmodified) with mlt_b200/lib/mlt/libmltcuda.so dropped into its repository, cfg4 command
             line, -consumer null real_time=-T; every frame is downloaded to (pinned) host memory.
-            Steady state = the difference of a short and a long run of the same process (removes
-            CUDA / MLT start-up, reported beside it).
+            Steady state from melt's own -progress2 position, timestamped as it arrives (start-up and
+            the draining of the render-ahead queue are outside the timed window, reported beside it).
+  e2e_resident  the same command line into -consumer cuda.null (device-frame hand-off, no download).
   e2e_abi   the round-1 end-to-end leg kept for comparison: pinned host tracks up, kernel, frame down
             through mltcuda_upload / _tractor / _download.
   extra     1080p device legs of cfg1 (composite), cfg2 (luma wipe), cfg3 (affine rgba), cfg4.
@@ -27,8 +28,8 @@ N > 1: one process per GPU (torchrun), frames shard by rank, no collective on th
 (frames are independent); timing is the max over ranks after a barrier.
 --impl reference: the UNMODIFIED reference (oracle/_ref/bin/melt, built from /root/reference by
 oracle/Makefile.ref) renders the same graph on the host cores with real_time=-nproc; a step is a
-bounded 32-frame sample of the 512-frame step, all steps rendered by one melt process, start-up removed
-with a second, shorter run.
+bounded 32-frame sample of the 512-frame step; warm-up and all steps are rendered by ONE melt process and
+timed from its -progress2 position, so process start-up is outside the timed window.
 """
 import argparse
 import ctypes as C
@@ -99,35 +100,53 @@ class Dist:
 
 # ---- melt runs (both arms) ------------------------------------------------------------------------------
 
-def melt_seconds(frames, threads, cuda, base, profile="uhd_2160p_60", graph=MELT_CFG4, extra=None):
-    """Wall time of one melt process rendering `frames` frames of the graph into -consumer null
-    (real_time=-threads: frame-parallel workers, never drops).  cuda=False: the stock services of the
-    reference; cuda=True: the same melt with libmltcuda.so in its repository.  Returns (seconds, stderr)."""
+def melt_run(frames, threads, cuda, base, warm, tail=96, profile="uhd_2160p_60", graph=MELT_CFG4, extra=None, consumer="null"):
+    """One melt process renders `frames` frames of the graph into -consumer null (real_time=-threads:
+    frame-parallel workers, never drops).  cuda=False: the stock services of the reference; cuda=True: the
+    same melt with libmltcuda.so in its repository.  melt's own -progress2 lines (its transport loop prints
+    the producer position every 40 ms, src/melt/melt.c:423-440,496) are timestamped as they arrive: the
+    steady-state rate is the position advance between the first sample past `warm` frames and the last one
+    before the final `tail` frames (the render-ahead queue draining), so start-up (CUDA / MLT initialisation)
+    and shut-down are outside the timed window.  Returns a dict."""
     env = meltenv.env(base, cuda=cuda, extra=extra)
     args = [a.format(last=frames - 1) for a in graph]
-    cmd = [meltenv.melt_binary(), "-profile", profile] + args + ["-consumer", "null", f"real_time=-{threads}", "-silent"]
+    cmd = [meltenv.melt_binary(), "-progress2", "-profile", profile] + args + ["-consumer", consumer, f"real_time=-{threads}",
+                                                                               "terminate_on_pause=1"]
     t0 = time.perf_counter()
-    r = subprocess.run(cmd, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True)
-    dt = time.perf_counter() - t0
-    if r.returncode:
-        raise SystemExit(f"bench.py: melt failed rc={r.returncode}: {r.stderr[-1500:]}")
-    return dt, r.stderr
+    p = subprocess.Popen(cmd, env=env, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, bufsize=1)
+    samples, other = [], []
+    for ln in p.stderr:
+        m = re.match(r"Current Frame:\s+(\d+)", ln)
+        if m:
+            samples.append((time.perf_counter() - t0, int(m.group(1))))
+        else:
+            other.append(ln)
+    rc = p.wait()
+    total = time.perf_counter() - t0
+    err = "".join(other)
+    if rc:
+        raise SystemExit(f"bench.py: melt failed rc={rc}: {err[-1500:]}")
+    win = [(t, n) for t, n in samples if warm <= n <= frames - tail]
+    if len(win) < 2 or win[-1][1] == win[0][1]:
+        raise SystemExit(f"bench.py: melt run too short to time ({len(samples)} progress samples for {frames} frames)")
+    (ta, na), (tb, nb) = win[0], win[-1]
+    return {"steady_fps": (nb - na) / (tb - ta), "whole_run_fps": frames / total, "startup_s": samples[0][0] if samples else None,
+            "window": (na, nb, round(tb - ta, 3)), "total_s": total, "frames": frames, "stderr": err}
 
 
-def melt_steady(n_short, n_long, threads, cuda, base, dist=None, **kw):
-    """Two runs of different length: (n_long - n_short) / (t_long - t_short) is the steady-state rate, the
-    rest of the short run is start-up.  With `dist`, every rank runs its own melt (one GPU each), barrier
-    before each run, and the times are the max over ranks."""
-    def one(n):
-        if dist:
-            dist.barrier()
-        t, err = melt_seconds(n, threads, cuda, base, **kw)
-        return (dist.reduce(t, "MAX") if dist else t), err
-    t_short, _ = one(n_short)
-    t_long, err = one(n_long)
-    steady = (n_long - n_short) / max(t_long - t_short, 1e-9)
-    return {"steady_fps": steady, "whole_run_fps": n_long / t_long, "startup_s": max(0.0, t_short - n_short / steady),
-            "t_short": t_short, "t_long": t_long, "n_short": n_short, "n_long": n_long, "stderr": err}
+def melt_steady(frames, warm, threads, cuda, base, dist=None, **kw):
+    """melt_run on every rank at once (one GPU each, barrier first); the aggregate rate is world x the
+    slowest rank's (= the work of all ranks over the longest time)."""
+    if dist:
+        dist.barrier()
+    r = melt_run(frames, threads, cuda, base, warm, **kw)
+    if dist:
+        r["steady_fps_min"] = dist.reduce(r["steady_fps"], "MIN")
+        r["whole_run_fps_min"] = dist.reduce(r["whole_run_fps"], "MIN")
+        r["startup_s_max"] = dist.reduce(r["startup_s"] or 0.0, "MAX")
+    else:
+        r["steady_fps_min"], r["whole_run_fps_min"], r["startup_s_max"] = r["steady_fps"], r["whole_run_fps"], r["startup_s"] or 0.0
+    return r
 
 
 def parse_cuda_stats(stderr):
@@ -146,35 +165,31 @@ def have_reference():
 
 # ---- reference arm ------------------------------------------------------------------------------------------
 
-def reference_fps(steps, warmup, cores, base):
-    """One melt process renders all `steps` samples back to back; a shorter run of `warmup` samples warms the
-    page cache and measures start-up."""
-    n_short = max(1, warmup) * REF_SAMPLE
-    n_long = n_short + steps * REF_SAMPLE
-    return melt_steady(n_short, n_long, cores, False, base)
+REF_TAIL = 64  # frames after the timed window: the render-ahead queue draining at the end of the run
 
 
 def run_reference(args, dist):
     if dist.rank != 0:
         return
+    if not have_reference():
+        raise SystemExit("bench.py --impl reference: oracle/_ref is not built (run __graft_entry__.build() where /root/reference exists)")
     cores = os.cpu_count() or 1
     base = tempfile.mkdtemp(prefix="mltbench_ref_")
-    if have_reference():
-        kind = "reference"
-        r = reference_fps(args.steps, args.warmup, cores, base)
-        fps = r["steady_fps"]
-        sample = (f"{REF_SAMPLE} of the {FRAMES_PER_STEP} frames of a step rendered; {args.steps} steps = one "
-                  f"oracle/_ref/bin/melt -consumer null real_time=-{cores} run of {r['n_long']} frames ({r['t_long']:.1f} s) "
-                  f"minus a {r['n_short']}-frame run ({r['t_short']:.1f} s): steady state, start-up {r['startup_s']:.2f} s "
-                  f"excluded; whole-run rate {r['whole_run_fps']:.2f} frames/s; CPU noise producers and mirror:flip included")
-        extra = {"whole_run_fps": round(r["whole_run_fps"], 3), "startup_s": round(r["startup_s"], 3)}
-    else:
-        raise SystemExit("bench.py --impl reference: oracle/_ref is not built (run __graft_entry__.build() where /root/reference exists)")
+    warm = max(1, args.warmup) * REF_SAMPLE
+    frames = warm + args.steps * REF_SAMPLE + REF_TAIL
+    r = melt_run(frames, cores, False, base, warm, tail=REF_TAIL)
+    fps = r["steady_fps"]
+    na, nb, dt = r["window"]
+    sample = (f"{REF_SAMPLE} of the {FRAMES_PER_STEP} frames of a step rendered; warm-up and all steps are ONE "
+              f"oracle/_ref/bin/melt -consumer null real_time=-{cores} run of {frames} frames ({r['total_s']:.1f} s wall); timed window = "
+              f"frames {na}..{nb} in {dt} s from melt's own -progress2 position (start-up {r['startup_s']:.2f} s and the final "
+              f"{REF_TAIL} frames excluded); whole-run rate {r['whole_run_fps']:.2f} frames/s; CPU noise producers and mirror:flip included")
     line = {"impl": "reference", "metric": METRIC, "value": round(fps, 3), "unit": "frames/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * FRAMES_PER_STEP / fps, 3),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": dict(CONFIG),
-            "cpu_baseline": dict({"value": round(fps, 3), "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample}, **extra),
+            "cpu_baseline": {"value": round(fps, 3), "unit": "frames/s", "cores": cores, "kind": "reference", "sample": sample,
+                             "whole_run_fps": round(r["whole_run_fps"], 3), "startup_s": round(r["startup_s"], 3)},
             "e2e": {"value": round(fps, 3), "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -502,36 +517,47 @@ def run_ours(args, dist):
         w_.sync()
     e2e = None
     threads = args.melt_threads or max(2, min(8, (os.cpu_count() or 8) // max(1, dist.world)))
+    e2e_resident = None
     if have_reference() and meltenv.have_module():
         base = tempfile.mkdtemp(prefix=f"mltbench_{dist.rank}_")
         ex = {"MLT_CUDA_DEVICE": str(dev), "MLT_CUDA_STATS": "1"}
-        r = melt_steady(args.melt_short, args.melt_short + args.melt_frames, threads, True, base, dist=dist, extra=ex)
+        r = melt_steady(args.melt_frames, args.melt_warm, threads, True, base, dist=dist, extra=ex)
         st = parse_cuda_stats(r["stderr"])
-        rendered = max(1, st.get("affine get_image (incl. inputs)", {}).get("calls", r["n_long"]))
+        rendered = max(1, st.get("affine get_image (incl. inputs)", {}).get("calls", r["frames"]))
         h2d = st.get("upload", {}).get("bytes", 0) / rendered
         d2h = st.get("download + sync", {}).get("bytes", 0) / rendered
-        e2e = {"value": round(dist.world * r["steady_fps"], 1), "unit": "frames/s",
+        na, nb, dt = r["window"]
+        e2e = {"value": round(dist.world * r["steady_fps_min"], 1), "unit": "frames/s",
                "h2d_bytes_per_step": int(dist.world * h2d * FRAMES_PER_STEP), "d2h_bytes_per_step": int(dist.world * d2h * FRAMES_PER_STEP),
                "path": f"oracle/_ref/bin/melt (unmodified MLT host) + mlt_b200/lib/mlt/libmltcuda.so, cfg4 command line, -consumer null "
-                       f"real_time=-{threads}, one melt per GPU",
-               "how": f"steady state: ({r['n_long']} - {r['n_short']}) frames / ({r['t_long']:.2f} - {r['t_short']:.2f}) s, max over ranks",
-               "whole_run_fps": round(dist.world * r["whole_run_fps"], 1), "startup_s": round(r["startup_s"], 2),
+                       f"real_time=-{threads}, one melt per GPU; every frame downloaded to pinned host memory",
+               "how": f"one run of {r['frames']} frames; timed window = frames {na}..{nb} in {dt} s from melt's -progress2 position "
+                      f"(rank 0's window shown; aggregate = world x the slowest rank)",
+               "whole_run_fps": round(dist.world * r["whole_run_fps_min"], 1), "startup_s": round(r["startup_s_max"], 2),
                "fused_launches_per_frame": round(st.get("fused pass (k_tractor launches)", {}).get("calls", 0) / rendered, 3),
                "unfused_compositing_launches": sum(st.get(k, {}).get("calls", 0) for k in
                                                    ("unfused composite launches", "unfused affine launches", "unfused luma launches")),
                "h2d_bytes_per_frame": int(h2d), "d2h_bytes_per_frame": int(d2h)}
+        # beside it, never instead of it: the same graph into the device-frame consumer -- no download
+        r2 = melt_steady(args.melt_frames, args.melt_warm, threads, True, base, dist=dist, extra=ex, consumer="cuda.null")
+        st2 = parse_cuda_stats(r2["stderr"])
+        e2e_resident = {"value": round(dist.world * r2["steady_fps_min"], 1), "unit": "frames/s",
+                        "path": "same melt command line with -consumer cuda.null: frames stay in HBM, the consumer waits on the frame's event",
+                        "d2h_bytes_per_frame": int(st2.get("download + sync", {}).get("bytes", 0) / rendered),
+                        "whole_run_fps": round(dist.world * r2["whole_run_fps_min"], 1)}
     elif e2e_abi:
         e2e = dict(e2e_abi, path="C-ABI only (no MLT install to host the module)")
 
     cpu = None
     if dist.rank == 0 and dist.world == 1 and not args.no_cpu_baseline and have_reference():
         cores = os.cpu_count() or 1
-        r = melt_steady(2 * REF_SAMPLE, 2 * REF_SAMPLE + 12 * REF_SAMPLE, cores, False, tempfile.mkdtemp(prefix="mltbench_cpu_"))
+        r = melt_run(2 * REF_SAMPLE + 12 * REF_SAMPLE + REF_TAIL, cores, False, tempfile.mkdtemp(prefix="mltbench_cpu_"), 2 * REF_SAMPLE,
+                     tail=REF_TAIL)
+        na, nb, dt = r["window"]
         cpu = {"value": round(r["steady_fps"], 3), "unit": "frames/s", "cores": cores, "kind": "reference",
                "whole_run_fps": round(r["whole_run_fps"], 3), "startup_s": round(r["startup_s"], 3),
-               "sample": f"{r['n_long'] - r['n_short']} frames of cfg4, steady state of oracle/_ref/bin/melt -consumer null "
-                         f"real_time=-{cores} ({r['n_long']}-frame run {r['t_long']:.1f} s minus {r['n_short']}-frame run "
-                         f"{r['t_short']:.1f} s), CPU noise producers and mirror:flip included"}
+               "sample": f"frames {na}..{nb} ({dt} s) of one {r['frames']}-frame oracle/_ref/bin/melt -consumer null real_time=-{cores} "
+                         f"run of cfg4 ({r['total_s']:.1f} s wall), CPU noise producers and mirror:flip included"}
 
     if dist.rank == 0:
         line = {"metric": METRIC, "value": round(value, 1), "unit": "frames/s", "n_gpus": dist.world,
@@ -544,6 +570,8 @@ def run_ours(args, dist):
                         "launches_per_frame": round(total_launches / (dist.world * FRAMES_PER_STEP * args.steps), 3),
                         "worker_streams": len(workers), "parallelism": f"frame-sharded x{dist.world}, no collective"},
                 "e2e": e2e, "gpu_launches": total_launches, "roofline": roofline, "clocks": clk}
+        if e2e_resident:
+            line["e2e_resident"] = e2e_resident
         if e2e_abi:
             line["e2e_abi"] = e2e_abi
         if extra:
@@ -632,8 +660,8 @@ def main():
     ap.add_argument("--no-e2e-abi", action="store_true", help="skip the C-ABI-only end-to-end leg")
     ap.add_argument("--streams", type=int, default=2, help="worker contexts (streams) per GPU on the device leg, 1..8")
     ap.add_argument("--melt-threads", type=int, default=0, help="real_time=-T of the melt + module leg (0 = auto)")
-    ap.add_argument("--melt-short", type=int, default=64, help="frames of the short (start-up) melt run")
-    ap.add_argument("--melt-frames", type=int, default=6000, help="frames the long melt run adds to the short one")
+    ap.add_argument("--melt-warm", type=int, default=1024, help="frames of the melt + module run before its timed window")
+    ap.add_argument("--melt-frames", type=int, default=12000, help="frames of the melt + module run")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     dist = Dist()

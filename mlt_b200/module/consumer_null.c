@@ -10,12 +10,14 @@
  * has no use for.
  *
  * This service is the stock `null` consumer with the hand-off contract such a sink follows:
- *   - "mlt_image_format" = private, so the workers ask for mlt_image_private;
  *   - on "consumer-frame-render" (fired by the worker right before it pulls, :1155) the frame is
- *     marked "_cuda_consumer": the outermost CUDA transition of the frame then runs the deferred
- *     op list before it returns (one fused launch, in the worker thread), records an event on the
- *     image and leaves the picture in HBM (mlt_tractor hands the tag "consumer.mlt_image_private"
- *     down to the track frames and the tagged handle up again, src/framework/mlt_tractor.c:372-410);
+ *     marked "consumer._cuda_consumer" (mlt_tractor copies "consumer." properties down to the track
+ *     frames, src/framework/mlt_tractor.c:372).  mlt_image_private cannot be requested through
+ *     "mlt_image_format" (it sorts after mlt_image_invalid, mlt_types.h:52-53, so
+ *     mlt_image_format_id never returns it): the workers keep asking for the host format, and the
+ *     module's converter, where the download would happen, honours the mark instead -- it runs the
+ *     deferred op list (one fused launch, in the worker thread), records an event on the image and
+ *     returns the frame still in format mlt_image_private;
  *   - on "consumer-frame-show" (the consumer thread, consumer_null.c:153) the sink waits for that
  *     event: the frame's pixels are final in HBM, nothing was copied.
  * Any other consumer can follow the same three steps.  A frame that reaches it with a host image
@@ -55,7 +57,6 @@ mlt_consumer cuda_consumer_null_init(mlt_profile profile, mlt_service_type type,
     if (!consumer)
         return NULL;
     mlt_properties props = MLT_CONSUMER_PROPERTIES(consumer);
-    mlt_properties_set(props, "mlt_image_format", "private");
     mlt_events_listen(props, consumer, "consumer-frame-render", (mlt_listener) on_frame_render);
     mlt_events_listen(props, consumer, "consumer-frame-show", (mlt_listener) on_frame_show);
     return consumer;

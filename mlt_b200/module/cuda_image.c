@@ -652,10 +652,12 @@ static int convert_image_impl(mlt_frame frame, uint8_t **image, mlt_image_format
         return 1; /* another module's request */
     if (ci && resident)
         return 0; /* stays in HBM; the asking service converts on the device if it must */
-    /* a device consumer (consumer_null.c) asked for mlt_image_private and one of our services
-     * answered: the picture stays in HBM, its deferred list has run (cuda_consumer_handoff) */
-    if (ci && output == mlt_image_private && mlt_properties_get_int(p, "consumer." CUDA_CONSUMER) > 0)
-        return 0;
+    /* Device-consumer hand-off (consumer_null.c): the consumer marked the frame, so the host format it
+     * nominally asks for (mlt_image_private cannot be named in "mlt_image_format": it sorts after
+     * mlt_image_invalid, mlt_types.h:52-53) is answered with the resident picture -- the deferred list
+     * runs here, in the worker thread, an event is recorded for the consumer, nothing is copied. */
+    if (ci && mlt_properties_get_int(p, "consumer." CUDA_CONSUMER) > 0 && mlt_properties_get_int(p, CUDA_REQUESTED) <= 0)
+        return cuda_image_mark_ready(ci);
 
     if (!ci) { /* host image */
         /* host -> host is the imageconvert filter's job, in the filter's place in the chain (the
@@ -724,17 +726,6 @@ static int cuda_imageconvert_image(mlt_frame frame, uint8_t **image, mlt_image_f
 void cuda_imageconvert_attach(mlt_frame frame)
 {
     mlt_frame_append_convert_image(frame, cuda_imageconvert_image);
-}
-
-/* Called by the CUDA transitions right before they return their image: when nobody of this module is
- * pulling (the request comes from outside) and the consumer declared that it takes device frames,
- * this is the hand-off -- the deferred list runs now and the event the consumer waits on is recorded. */
-int cuda_consumer_handoff(mlt_frame frame, cuda_image ci)
-{
-    mlt_properties p = MLT_FRAME_PROPERTIES(frame);
-    if (mlt_properties_get_int(p, CUDA_REQUESTED) > 0 || mlt_properties_get_int(p, "consumer." CUDA_CONSUMER) <= 0)
-        return 0;
-    return cuda_image_mark_ready(ci);
 }
 
 /* ---- pulling inputs ------------------------------------------------------------------------------------ */

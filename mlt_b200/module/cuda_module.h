@@ -108,7 +108,6 @@ int cuda_image_flush(cuda_image a);
 /* Device-consumer hand-off: run the pending ops and record `ready` behind them / wait for it. */
 int cuda_image_mark_ready(cuda_image a);
 int cuda_image_wait_ready(cuda_image a);
-int cuda_consumer_handoff(mlt_frame frame, cuda_image ci); /* see cuda_image.c */
 /* Will the image have an alpha plane once its pending ops have run? */
 int cuda_image_has_alpha(cuda_image a);
 /* Make `b` (materialised) readable by kernels launched on `ctx`: same context -> nothing; same GPU,

@@ -376,7 +376,7 @@ out:
     /* drop the (potentially large) B image: stream-ordered free, safe after the launch */
     mlt_frame_set_image(b_frame, NULL, 0, NULL);
     mlt_properties_set(b_props, CUDA_IMAGE_TAG, NULL);
-    return rc ? rc : cuda_consumer_handoff(a_frame, a);
+    return rc;
 }
 
 static int affine_get_image(mlt_frame a_frame, uint8_t **image, mlt_image_format *format, int *width, int *height, int writable)

@@ -475,7 +475,7 @@ done:
         return 1;
     *image = (uint8_t *) a, *format = mlt_image_private;
     *width = a->width, *height = a->height;
-    return cuda_consumer_handoff(a_frame, a);
+    return 0;
 }
 
 static int composite_get_image(mlt_frame a_frame, uint8_t **image, mlt_image_format *format, int *width, int *height, int writable)

@@ -270,7 +270,7 @@ static int luma_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_for
         mlt_properties_set(a_props, CUDA_IMAGE_TAG, CUDA_IMAGE_TAG_VALUE);
     *image = (uint8_t *) dst, *format = mlt_image_private;
     *width = dst->width, *height = dst->height;
-    return cuda_consumer_handoff(a_frame, dst);
+    return 0;
 }
 
 static int luma_get_image(mlt_frame a_frame, uint8_t **image, mlt_image_format *format, int *width, int *height, int writable)

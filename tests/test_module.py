@@ -453,4 +453,5 @@ def test_cuda_null_consumer_takes_device_frames(tmp_path):
     frames = stats.get("affine get_image (incl. inputs)")
     assert frames and frames >= n, (stats, r.stderr[-1500:])
     assert "download + sync" not in stats and "upload" not in stats, stats
-    assert stats.get("fused pass (k_tractor launches)") == frames, stats
+    # (frames melt pulls again while it stops are dropped before their hand-off)
+    assert n <= stats.get("fused pass (k_tractor launches)") <= frames, stats
