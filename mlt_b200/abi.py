@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libmltcuda_rt.so")
+LIB_PATH = os.environ.get("MLTCUDA_RT_LIB") or os.path.join(HERE, "lib", "libmltcuda_rt.so")  # (override: A/B builds of tools/ab.sh)
 
 FMT_RGB, FMT_RGBA, FMT_YUV422, FMT_YUV420P, FMT_RGBA64 = 1, 2, 3, 4, 10
 OP_OVER, OP_OR, OP_AND, OP_XOR = 0, 1, 2, 3

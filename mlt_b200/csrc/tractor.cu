@@ -22,6 +22,8 @@ struct TCompOp
     const uint8_t *src, *alpha_b;
     const uint16_t *luma;
     int x, y, rows, row_step;
+    unsigned y_span, x_span; // rows / columns (+7) the rectangle spans in the frame
+    int row_mask, row_shift; // field stepping: (row_step == 2) ? 1 : 0
     long stride_src, stride_ab;
     size_t src_bs, ab_bs, luma_bs;
 };
@@ -85,8 +87,11 @@ __host__ __device__ constexpr int sig_first(uint32_t sig, uint32_t code)
     return -1;
 }
 
+#ifndef K5_MINB
+#define K5_MINB 8
+#endif
 template <bool ONLY_BL, uint32_t SIG>
-__global__ void __launch_bounds__(128, ONLY_BL ? 8 : 2) k_tractor(const __grid_constant__ TractorK K)
+__global__ void __launch_bounds__(128, ONLY_BL ? K5_MINB : 2) k_tractor(const __grid_constant__ TractorK K)
 {
     // 2-D CTA: 32 groups (256 px) x 4 rows (128-thread CTAs balance the heavy affine tiles better than 256: +2.8%) -- no div/mod, and the B taps of neighbouring rows share L1
     const int c = blockIdx.x * 32 + threadIdx.x;
@@ -147,13 +152,12 @@ __global__ void __launch_bounds__(128, ONLY_BL ? 8 : 2) k_tractor(const __grid_c
                              : (op.kind == MLTCUDA_TOP_CONVERT ? (op.to_format == MLTCUDA_FMT_RGBA ? 4 : 5) : op.kind);
         if (code == 1) {
             const TCompOp &C = op.c;
-            int rrel = r - C.y;
-            if (rrel < 0 || (C.row_step == 2 && (rrel & 1)))
+            // is this group inside the rectangle?  one unsigned compare per axis (y_span / x_span are set by the host)
+            const int rrel = r - C.y;
+            const int j0 = col0 - C.x;
+            if ((unsigned) rrel >= C.y_span || (unsigned) (j0 + 7) >= C.x_span || (rrel & C.row_mask))
                 continue;
-            int rr = C.row_step == 2 ? rrel >> 1 : rrel;
-            int j0 = col0 - C.x;
-            if (rr >= C.rows || j0 + 8 <= 0 || j0 >= C.cp.width)
-                continue;
+            const int rr = rrel >> C.row_shift;
             int jlo = j0 < 0 ? 0 : j0, jhi = j0 + 8 > C.cp.width ? C.cp.width : j0 + 8;
             uint32_t s[4], ab[2] = {0, 0}, lum[4] = {0, 0, 0, 0};
             uintptr_t srow = (uintptr_t) (C.src + b * C.src_bs + rr * C.stride_src);
@@ -387,6 +391,9 @@ extern "C" int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d)
             MC_BADARG(cd.stride_dest != rowb && cd.stride_dest != 2 * rowb, "composite stride_dest must be 1 or 2 rows");
             t.c.row_step = (int) (cd.stride_dest / rowb);
             t.c.rows = cd.rows;
+            t.c.row_shift = t.c.row_mask = t.c.row_step == 2 ? 1 : 0;
+            t.c.y_span = (unsigned) ((cd.rows - 1) * t.c.row_step + 1);
+            t.c.x_span = (unsigned) (cd.width + 7);
             t.c.src = cd.src, t.c.alpha_b = cd.alpha_b, t.c.luma = cd.luma;
             t.c.stride_src = cd.stride_src, t.c.stride_ab = cd.stride_alpha_b;
             t.c.src_bs = cd.src_bstride, t.c.ab_bs = cd.alpha_b_bstride, t.c.luma_bs = cd.luma_bstride;
