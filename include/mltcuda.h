@@ -92,6 +92,13 @@ int mltcuda_upload_staged(mltcuda_ctx *ctx, void *dst_dev, const void *src_host,
 int mltcuda_copy(mltcuda_ctx *ctx, void *dst_dev, const void *src_dev, size_t bytes);
 int mltcuda_memset(mltcuda_ctx *ctx, void *dst_dev, int value, size_t bytes);
 
+/* Is every byte of a device plane 0xff?  -- is_opaque() of src/modules/core/transition_luma.c:34-41 as a
+ * stream-ordered query: _query enqueues the reduction and the copy of its verdict to pinned host
+ * memory; after the next mltcuda_ctx_sync / event wait behind it, _result returns 1 (all 0xff) or 0.
+ * Lets the host write an opaque alpha plane itself instead of copying it over PCIe. */
+int mltcuda_plane_opaque_query(mltcuda_ctx *ctx, const uint8_t *plane_dev, size_t bytes);
+int mltcuda_plane_opaque_result(const mltcuda_ctx *ctx);
+
 /* CUDA-event timing on the context stream (used by bench.py; torch events do not see it). */
 typedef struct mltcuda_event mltcuda_event;
 mltcuda_event *mltcuda_event_create(void);

@@ -101,6 +101,8 @@ SIGNATURES = {
     "mltcuda_download": (C.c_int, [vp, vp, vp, sz]),
     "mltcuda_copy": (C.c_int, [vp, vp, vp, sz]),
     "mltcuda_memset": (C.c_int, [vp, vp, C.c_int, sz]),
+    "mltcuda_plane_opaque_query": (C.c_int, [vp, vp, sz]),
+    "mltcuda_plane_opaque_result": (C.c_int, [vp]),
     "mltcuda_event_create": (vp, []),
     "mltcuda_event_destroy": (None, [vp]),
     "mltcuda_event_record": (C.c_int, [vp, vp]),

@@ -17,6 +17,8 @@ struct mltcuda_ctx
     void *stage[2];
     cudaEvent_t stage_done[2];
     int stage_next;
+    // opacity query (mltcuda_plane_opaque_query): device flag + its pinned host mirror
+    int *opaque_dev, *opaque_host;
 };
 #define MLTCUDA_STAGE_BYTES (4u << 20)
 

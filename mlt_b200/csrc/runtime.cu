@@ -64,6 +64,7 @@ mltcuda_ctx *mltcuda_ctx_create(int device)
     ctx->launches = 0;
     ctx->noise_tab = nullptr;
     ctx->stage[0] = ctx->stage[1] = nullptr, ctx->stage_next = 0;
+    ctx->opaque_dev = ctx->opaque_host = nullptr;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
         mltcuda_set_error("cudaStreamCreate failed: %s", cudaGetErrorString(cudaGetLastError()));
         delete ctx;
@@ -85,6 +86,10 @@ void mltcuda_ctx_destroy(mltcuda_ctx *ctx)
     cudaStreamSynchronize(ctx->stream);
     if (ctx->noise_tab)
         cudaFree(ctx->noise_tab);
+    if (ctx->opaque_dev)
+        cudaFree(ctx->opaque_dev);
+    if (ctx->opaque_host)
+        cudaFreeHost(ctx->opaque_host);
     for (int i = 0; i < 2; i++)
         if (ctx->stage[i]) {
             cudaFreeHost(ctx->stage[i]);
@@ -290,6 +295,49 @@ int mltcuda_memset(mltcuda_ctx *ctx, void *dst, int value, size_t bytes)
         return e;
     MC_CHECK(cudaMemsetAsync(dst, value, bytes, ctx->stream));
     return 0;
+}
+
+// is_opaque() of the reference (src/modules/core/transition_luma.c:34-41) as a stream-ordered query:
+// a plane whose every byte is 0xff need not cross PCIe, the host can write it itself.
+namespace {
+__global__ void __launch_bounds__(256) k_plane_not_ff(const uint4 *p, size_t n16, const uint8_t *tail, int ntail, int *flag)
+{
+    size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t step = (size_t) gridDim.x * blockDim.x;
+    uint32_t acc = 0xffffffffu;
+    for (; i < n16; i += step) {
+        const uint4 v = __ldg(p + i);
+        acc &= v.x & v.y & v.z & v.w;
+    }
+    if (blockIdx.x == 0 && (int) threadIdx.x < ntail)
+        acc &= 0xffffff00u | tail[threadIdx.x];
+    if (__any_sync(0xffffffffu, acc != 0xffffffffu) && (threadIdx.x & 31) == 0)
+        *flag = 1;
+}
+} // namespace
+
+int mltcuda_plane_opaque_query(mltcuda_ctx *ctx, const uint8_t *plane, size_t bytes)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!plane || ((uintptr_t) plane & 15), "plane must be a 16-byte aligned device pointer");
+    if (!ctx->opaque_dev) {
+        MC_CHECK(cudaMalloc(&ctx->opaque_dev, sizeof(int)));
+        MC_CHECK(cudaHostAlloc(&ctx->opaque_host, sizeof(int), cudaHostAllocPortable));
+    }
+    MC_CHECK(cudaMemsetAsync(ctx->opaque_dev, 0, sizeof(int), ctx->stream));
+    const size_t n16 = bytes / 16;
+    k_plane_not_ff<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>((const uint4 *) plane, n16, plane + n16 * 16, (int) (bytes - n16 * 16),
+                                                             ctx->opaque_dev);
+    if (int e = mc_after_launch(ctx, "k_plane_not_ff"))
+        return e;
+    MC_CHECK(cudaMemcpyAsync(ctx->opaque_host, ctx->opaque_dev, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    return 0;
+}
+
+int mltcuda_plane_opaque_result(const mltcuda_ctx *ctx)
+{
+    return ctx && ctx->opaque_host ? *ctx->opaque_host == 0 : 0;
 }
 
 mltcuda_event *mltcuda_event_create(void)

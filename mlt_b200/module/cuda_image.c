@@ -468,14 +468,37 @@ int cuda_download_to_frame(mlt_frame frame, cuda_image ci, uint8_t **image, mlt_
             mltcuda_host_pool_release(ahost);
         return 1;
     }
+    /* An alpha plane that is 0xff everywhere (the usual case: the rgba -> yuv422 conversion of an opaque
+     * picture creates one, filter_imageconvert.c:144-184) does not cross PCIe: the device answers
+     * is_opaque() behind the image copy and the host writes the plane itself (a third of the bytes of a
+     * yuv422 frame).  MLT_CUDA_ALPHA_DMA=1 forces the copy. */
+    static int alpha_dma = -1;
+    if (alpha_dma < 0) {
+        const char *e = getenv("MLT_CUDA_ALPHA_DMA");
+        alpha_dma = e && *e && *e != '0';
+    }
     int rc = mltcuda_download(ci->ctx, host, ci->data, bytes);
-    if (!rc && abytes)
+    const int query = !rc && abytes && !alpha_dma && !((uintptr_t) ci->alpha & 15);
+    if (query)
+        rc = mltcuda_plane_opaque_query(ci->ctx, ci->alpha, abytes);
+    else if (!rc && abytes)
         rc = mltcuda_download(ci->ctx, ahost, ci->alpha, abytes);
     if (!rc)
         rc = mltcuda_ctx_sync(ci->ctx);
+    size_t moved = bytes + abytes;
+    if (!rc && query) {
+        if (mltcuda_plane_opaque_result(ci->ctx)) {
+            memset(ahost, 0xff, abytes);
+            moved = bytes;
+        } else {
+            rc = mltcuda_download(ci->ctx, ahost, ci->alpha, abytes);
+            if (!rc)
+                rc = mltcuda_ctx_sync(ci->ctx);
+        }
+    }
     CUDA_STAT_END(CS_DOWNLOAD, st0);
     if (cuda_stats_on)
-        cuda_stat_bytes(CS_DOWNLOAD, bytes + abytes);
+        cuda_stat_bytes(CS_DOWNLOAD, moved);
     if (rc) {
         mlt_log_error(NULL, "[cuda] download failed: %s\n", mltcuda_last_error());
         if (host)

@@ -58,3 +58,21 @@ def test_wait_event_orders_two_contexts(ctx):
         other.sync()
         assert int(ctx.get(b, (n,)).min()) == value and int(ctx.get(b, (n,)).max()) == value
     lib.mltcuda_event_destroy(ev)
+
+
+@pytest.mark.parametrize("nbytes", [1, 15, 16, 17, 1920 * 1080, 3840 * 2160 + 5])
+def test_plane_opaque_query(ctx, nbytes):
+    """is_opaque() (transition_luma.c:34-41) as a stream-ordered device query: all 0xff <=> opaque, any position."""
+    lib = ctx.lib
+    plane = np.full(nbytes, 0xff, np.uint8)
+    d = ctx.put(plane)
+    abi.check(lib.mltcuda_plane_opaque_query(ctx.h, d.ptr, nbytes))
+    ctx.sync()
+    assert lib.mltcuda_plane_opaque_result(ctx.h) == 1
+    for pos in sorted({0, nbytes // 2, nbytes - 1}):
+        p2 = plane.copy()
+        p2[pos] = 0xfe
+        d2 = ctx.put(p2)
+        abi.check(lib.mltcuda_plane_opaque_query(ctx.h, d2.ptr, nbytes))
+        ctx.sync()
+        assert lib.mltcuda_plane_opaque_result(ctx.h) == 0, pos
