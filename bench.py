@@ -488,10 +488,12 @@ def run_ours(args, dist):
     except OSError:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+    winstr = sms = None
     traffic = dram_read = None  # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed ncu --set full capture
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "k_tractor_traffic.json")))
         traffic, dram_read = tj["dram_bytes_per_launch"], tj.get("dram_read_bytes")
+        winstr, sms = tj.get("warp_instructions_per_launch"), tj.get("sm_count", 148)
     except (OSError, KeyError, ValueError):
         pass
     # measured DRAM reads (ncu) + the bytes the kernel stores (most of a launch's stores are still in
@@ -505,6 +507,13 @@ def run_ours(args, dist):
                 "algorithmic_bytes_per_launch": int(alg_per_launch),
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s"}
 
+    # The kernel is issue-bound: the instruction-issue roofline beside the HBM one.  Warp instructions per
+    # launch come from the committed ncu capture (smsp__inst_executed.sum); 4 schedulers per SM issue one each per cycle.
+    if winstr and clk.get("sm_mhz"):
+        min_us = winstr / (sms * 4 * clk["sm_mhz"] * 1e6) * 1e6
+        roofline["issue_bound"] = {"warp_instr_per_launch": winstr, "min_us_per_launch": round(min_us, 2),
+                                   "frac": round(min_us / (avg_launch_s * 1e6), 4),
+                                   "hbm_frac_at_full_issue": round(alg_per_launch / (min_us * 1e-6) / 1e9 / peak, 4)}
     extra = extra_1080p(lib, ctx, workers, dist, max(2, min(5, args.steps))) if not args.no_extra else None
 
     # ---- end to end through the C-ABI: host (pinned) tracks in, composited frame out ------------------
