@@ -29,25 +29,23 @@ struct CompK
     int cpr; // chunks per row upper bound
 };
 
-// BLIT: P.blit (SSE2 cases 0/4), a separate instantiation so the blend cases keep their exact code
-template <bool BLIT> __global__ void __launch_bounds__(256, 8) k_composite_rows(CompK K)
+// One 16-byte-aligned group `c` of row `r` of frame `b`.  EDGE = false: whole groups only (all 8 pixels inside the
+// row, one formula) -- the per-pixel code is compiled out and ragged groups are left to the EDGE = true pass.
+// BLIT: P.blit (SSE2 cases 0/4), a separate instantiation so the blend cases keep their exact code.
+template <bool BLIT, bool EDGE> __device__ __forceinline__ void composite_group(const CompK &K, int c, int r, int b)
 {
-    // grid = (chunks of a row, row, frame): no div/mod in the index math
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= K.cpr)
-        return;
-    const int r = blockIdx.y, b = blockIdx.z;
     const CompositeParams &P = K.p;
-
     uintptr_t drow = (uintptr_t) (K.dest + b * K.dest_bs + r * K.stride_dest);
     int head = (int) ((drow & 15) >> 1);      // pixels between the aligned address and the row start
     int j0 = c * 8 - head;                    // row-relative index of the group's first pixel
     if (j0 >= P.width)
         return;
     int jlo = j0 < 0 ? 0 : j0, jhi = j0 + 8 > P.width ? P.width : j0 + 8; // valid [jlo, jhi)
+    if (mc_composite_group_is_whole(P, j0, jlo, jhi) == EDGE)
+        return; // the other pass owns this group
     uint4 *dptr = reinterpret_cast<uint4 *>(drow + 2 * (long) j0);        // 16-byte aligned
     // a whole group of a blit (SSE2 cases 0/4: memcpy + memset) overwrites A: do not read it
-    const bool overwrite = BLIT && jlo == j0 && jhi == j0 + 8;
+    const bool overwrite = BLIT && !EDGE;
     uint4 dv = make_uint4(0, 0, 0, 0);
     if (!overwrite)
         dv = ld16(dptr);
@@ -68,7 +66,7 @@ template <bool BLIT> __global__ void __launch_bounds__(256, 8) k_composite_rows(
         // read-modify-write: coherent byte/vector loads (no __ldg)
         uintptr_t a = (uintptr_t) aarow + j0;
         if (overwrite) {
-        } else if ((a & 7) == 0 && jlo == j0 && jhi == j0 + 8) {
+        } else if (!EDGE && (a & 7) == 0) {
             uint2 v = ld8((const void *) a);
             aa[0] = v.x, aa[1] = v.y;
         } else {
@@ -83,9 +81,9 @@ template <bool BLIT> __global__ void __launch_bounds__(256, 8) k_composite_rows(
         fetch16(lrow + 2 * (long) j0, lrow + 2 * (long) jlo, lrow + 2 * (long) jhi, lum);
     }
 
-    mc_composite_group8(P, j0, jlo, jhi, d, s, ab, aa, lum);
+    mc_composite_group8<true, EDGE>(P, j0, jlo, jhi, d, s, ab, aa, lum);
     const uint32_t *o = d, *oa = aa;
-    if (jlo == j0 && jhi == j0 + 8) {
+    if (!EDGE) {
         *dptr = make_uint4(o[0], o[1], o[2], o[3]);
     } else {
         uint16_t *d16 = reinterpret_cast<uint16_t *>(dptr);
@@ -96,7 +94,7 @@ template <bool BLIT> __global__ void __launch_bounds__(256, 8) k_composite_rows(
     }
     if (P.has_aa) {
         uintptr_t a = (uintptr_t) aarow + j0;
-        if ((a & 7) == 0 && jlo == j0 && jhi == j0 + 8) {
+        if (!EDGE && (a & 7) == 0) {
             *reinterpret_cast<uint2 *>(a) = make_uint2(oa[0], oa[1]);
         } else {
 #pragma unroll
@@ -105,6 +103,41 @@ template <bool BLIT> __global__ void __launch_bounds__(256, 8) k_composite_rows(
                     aarow[j0 + k] = (uint8_t) (oa[k >> 2] >> ((k & 3) * 8));
         }
     }
+}
+
+// interior pass: grid = (groups of a row, row, frame): no div/mod in the index math
+template <bool BLIT> __global__ void __launch_bounds__(256, 8) k_composite_rows(CompK K)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= K.cpr)
+        return;
+    composite_group<BLIT, false>(K, c, blockIdx.y, blockIdx.z);
+}
+
+// Edge pass: the (at most three) groups of a row that are not whole -- the ragged first and last group of a
+// rectangle that does not start / end on a 16-byte boundary of A, and the group that straddles the SSE2 / scalar
+// boundary n8.  Each takes the per-pixel path (several hundred instructions); inside the interior
+// kernel one such lane per row end kept its whole warp waiting (70 % of the instructions of a narrow rectangle at
+// an odd x, profiles/r1l_weak_1).  Here every lane of a warp is a ragged group of a different row.
+template <bool BLIT> __global__ void __launch_bounds__(128) k_composite_edges(CompK K)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= K.rows)
+        return;
+    const int b = blockIdx.z, e = blockIdx.y; // e: 0 first group, 1 the n8 straddler, 2 last group
+    const uintptr_t drow = (uintptr_t) (K.dest + b * K.dest_bs + r * K.stride_dest);
+    const int head = (int) ((drow & 15) >> 1);
+    const int c_last = (head + K.p.width - 1) >> 3, c_mid = (head + K.p.n8) >> 3;
+    int c;
+    if (e == 0)
+        c = 0;
+    else if (e == 2)
+        c = c_last;
+    else
+        c = c_mid;
+    if ((e == 2 && c_last == 0) || (e == 1 && (c_mid == 0 || c_mid >= c_last)))
+        return; // same group as an earlier e
+    composite_group<BLIT, true>(K, c, r, b); // returns at once when the group is whole
 }
 
 } // namespace
@@ -154,7 +187,19 @@ extern "C" int mltcuda_composite(mltcuda_ctx *ctx, const mltcuda_composite_desc 
         k_composite_rows<true><<<grd, 128, 0, ctx->stream>>>(K);
     else
         k_composite_rows<false><<<grd, 128, 0, ctx->stream>>>(K);
-    return mc_after_launch(ctx, "k_composite_rows");
+    if (int e = mc_after_launch(ctx, "k_composite_rows"))
+        return e;
+    // Ragged groups exist unless every row starts on a 16-byte boundary of A and the width is a multiple of 8
+    // (then n8 == width or 0 and every group is whole).
+    const bool aligned = ((uintptr_t) d->dest & 15) == 0 && (d->stride_dest & 15) == 0 && (K.dest_bs & 15) == 0 && d->width % 8 == 0;
+    if (aligned)
+        return 0;
+    dim3 egrd((K.rows + 127) / 128, 3, K.batch);
+    if (K.p.blit)
+        k_composite_edges<true><<<egrd, 128, 0, ctx->stream>>>(K);
+    else
+        k_composite_edges<false><<<egrd, 128, 0, ctx->stream>>>(K);
+    return mc_after_launch(ctx, "k_composite_edges");
 }
 
 // Host restatement of the integer clipping in composite_yuv (transition_composite.c:345-452).
