@@ -17,29 +17,63 @@
 
 #define MAX_CTX 256
 static pthread_mutex_t g_ctx_lock = PTHREAD_MUTEX_INITIALIZER;
-static mltcuda_ctx *g_ctx[MAX_CTX];
+static mltcuda_ctx *g_ctx[MAX_CTX];      /* every context ever created (for the launch totals) */
 static int g_ctx_count = 0;
+static mltcuda_ctx *g_idle[MAX_CTX];     /* contexts whose worker thread has exited: re-used, never destroyed */
+static int g_idle_count = 0;
+static pthread_key_t g_ctx_key;
+static pthread_once_t g_ctx_key_once = PTHREAD_ONCE_INIT;
 static __thread mltcuda_ctx *t_ctx = NULL;
 static __thread int t_ctx_failed = 0;
+
+/* A worker thread ends (MLT consumers spawn new workers on every start / stop): its context goes back
+ * to the idle list.  It is not destroyed -- frames it produced may still be queued in the consumer and
+ * free their buffers through it -- but the next worker thread takes it over instead of creating another
+ * stream + pinned staging, so a long-lived host (an editor restarting its consumer) does not grow. */
+static void ctx_thread_exit(void *c)
+{
+    pthread_mutex_lock(&g_ctx_lock);
+    if (c && g_idle_count < MAX_CTX)
+        g_idle[g_idle_count++] = c;
+    pthread_mutex_unlock(&g_ctx_lock);
+}
+
+static void ctx_key_init(void)
+{
+    pthread_key_create(&g_ctx_key, ctx_thread_exit);
+}
 
 mltcuda_ctx *cuda_thread_ctx(void)
 {
     if (t_ctx || t_ctx_failed)
         return t_ctx;
     const char *dev = getenv("MLT_CUDA_DEVICE"); /* pin every worker to one GPU; default round-robin */
-    const uint64_t st0 = CUDA_STAT_T0();
-    mltcuda_ctx *c = mltcuda_ctx_create(dev && *dev ? atoi(dev) : -1);
-    CUDA_STAT_END(CS_CTX_CREATE, st0);
-    if (!c) {
-        t_ctx_failed = 1;
-        mlt_log_error(NULL, "[cuda] no usable CUDA device: %s (this module has no CPU fallback)\n", mltcuda_last_error());
-        return NULL;
-    }
+    const int want = dev && *dev ? atoi(dev) : -1;
+    pthread_once(&g_ctx_key_once, ctx_key_init);
+    mltcuda_ctx *c = NULL;
     pthread_mutex_lock(&g_ctx_lock);
-    if (g_ctx_count < MAX_CTX)
-        g_ctx[g_ctx_count++] = c; /* kept until process exit: frames may outlive their worker */
+    for (int i = g_idle_count - 1; i >= 0 && !c; i--)
+        if (want < 0 || mltcuda_ctx_device(g_idle[i]) == want) {
+            c = g_idle[i];
+            g_idle[i] = g_idle[--g_idle_count];
+        }
     pthread_mutex_unlock(&g_ctx_lock);
-    mlt_log_verbose(NULL, "[cuda] worker context %d on GPU %d\n", g_ctx_count, mltcuda_ctx_device(c));
+    if (!c) {
+        const uint64_t st0 = CUDA_STAT_T0();
+        c = mltcuda_ctx_create(want);
+        CUDA_STAT_END(CS_CTX_CREATE, st0);
+        if (!c) {
+            t_ctx_failed = 1;
+            mlt_log_error(NULL, "[cuda] no usable CUDA device: %s (this module has no CPU fallback)\n", mltcuda_last_error());
+            return NULL;
+        }
+        pthread_mutex_lock(&g_ctx_lock);
+        if (g_ctx_count < MAX_CTX)
+            g_ctx[g_ctx_count++] = c;
+        pthread_mutex_unlock(&g_ctx_lock);
+        mlt_log_verbose(NULL, "[cuda] worker context %d on GPU %d\n", g_ctx_count, mltcuda_ctx_device(c));
+    }
+    pthread_setspecific(g_ctx_key, c);
     t_ctx = c;
     return c;
 }
@@ -826,7 +860,7 @@ typedef struct
     mltcuda_ctx *ctx;
     uint16_t *dev;
     const uint16_t *host;
-    int w, h;
+    int w, h, generation;
 } map_cache;
 
 static void map_cache_close(void *ptr)
@@ -839,17 +873,20 @@ static void map_cache_close(void *ptr)
     }
 }
 
-uint16_t *cuda_cached_map(mlt_properties owner, const char *key, mltcuda_ctx *ctx, const uint16_t *host, int w, int h)
+/* `generation` counts the replacements of the host map (the owner bumps it whenever it installs a new
+ * bitmap): mlt_pool recycles same-size blocks, so pointer + size alone cannot tell a regenerated map
+ * from the one a context uploaded earlier. */
+uint16_t *cuda_cached_map(mlt_properties owner, const char *key, mltcuda_ctx *ctx, const uint16_t *host, int w, int h, int generation)
 {
     char name[96];
     snprintf(name, sizeof(name), "_cuda.%s.%p", key, (void *) ctx);
     map_cache *m = mlt_properties_get_data(owner, name, NULL);
-    if (m && m->host == host && m->w == w && m->h == h)
+    if (m && m->host == host && m->w == w && m->h == h && m->generation == generation)
         return m->dev;
     m = calloc(1, sizeof(*m));
     if (!m)
         return NULL;
-    m->ctx = ctx, m->host = host, m->w = w, m->h = h;
+    m->ctx = ctx, m->host = host, m->w = w, m->h = h, m->generation = generation;
     m->dev = mltcuda_malloc(ctx, (size_t) w * h * 2);
     if (!m->dev || mltcuda_upload(ctx, m->dev, host, (size_t) w * h * 2) || mltcuda_ctx_sync(ctx)) {
         map_cache_close(m);

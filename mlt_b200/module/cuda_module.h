@@ -152,9 +152,10 @@ void cuda_imageconvert_attach(mlt_frame frame);
 /* true if a device producer may answer this request with a resident image */
 int cuda_request_resident(mlt_frame frame, mlt_image_format requested);
 
-/* Device copy of a host uint16 luma map, cached on `owner` under `key` until the host pointer or
- * the size changes. */
-uint16_t *cuda_cached_map(mlt_properties owner, const char *key, mltcuda_ctx *ctx, const uint16_t *host, int w, int h);
+/* Device copy of a host uint16 luma map, cached per context on `owner` under `key` until the host pointer,
+ * the size or `generation` (bumped by the owner whenever it replaces the map) changes. */
+#define CUDA_MAP_GENERATION "_cuda_map_generation"
+uint16_t *cuda_cached_map(mlt_properties owner, const char *key, mltcuda_ctx *ctx, const uint16_t *host, int w, int h, int generation);
 
 /* --- constructors (one file per service) ---------------------------------------------------- */
 mlt_producer cuda_producer_noise_init(mlt_profile, mlt_service_type, const char *, char *);

@@ -163,7 +163,7 @@ typedef struct
     mltcuda_ctx *ctx;
     uint16_t *dev;
     const uint16_t *orig;
-    int w, h, invert;
+    int w, h, invert, generation;
 } scaled_map;
 
 static void scaled_map_close(void *ptr)
@@ -244,6 +244,7 @@ static uint16_t *host_luma(mlt_transition self, int *lw, int *lh)
     }
     if (!orig || *lw <= 0 || *lh <= 0)
         return NULL;
+    mlt_properties_set_int(props, CUDA_MAP_GENERATION, mlt_properties_get_int(props, CUDA_MAP_GENERATION) + 1);
     mlt_properties_set_data(props, "_luma.orig_bitmap", orig, *lw * *lh * 2, mlt_pool_release, NULL);
     mlt_properties_set_int(props, "_luma.orig_width", *lw);
     mlt_properties_set_int(props, "_luma.orig_height", *lh);
@@ -263,15 +264,16 @@ static uint16_t *device_luma(mlt_transition self, mltcuda_ctx *ctx, int width, i
     char name[64];
     snprintf(name, sizeof(name), "_cuda.luma.%p", (void *) ctx);
     scaled_map *m = mlt_properties_get_data(props, name, NULL);
-    if (m && m->orig == orig && m->w == width && m->h == height && m->invert == invert)
+    const int generation = mlt_properties_get_int(props, CUDA_MAP_GENERATION);
+    if (m && m->orig == orig && m->w == width && m->h == height && m->invert == invert && m->generation == generation)
         return m->dev;
-    uint16_t *dorig = cuda_cached_map(props, "luma.orig", ctx, orig, lw, lh);
+    uint16_t *dorig = cuda_cached_map(props, "luma.orig", ctx, orig, lw, lh, mlt_properties_get_int(props, CUDA_MAP_GENERATION));
     if (!dorig)
         return NULL;
     m = calloc(1, sizeof(*m));
     if (!m)
         return NULL;
-    m->ctx = ctx, m->orig = orig, m->w = width, m->h = height, m->invert = invert;
+    m->ctx = ctx, m->orig = orig, m->w = width, m->h = height, m->invert = invert, m->generation = generation;
     m->dev = mltcuda_malloc(ctx, (size_t) width * height * 2);
     if (!m->dev || mltcuda_scale_luma(ctx, m->dev, width, height, dorig, lw, lh, invert * 0xffff)) {
         mlt_log_error(MLT_TRANSITION_SERVICE(self), "luma map scaling failed: %s\n", mltcuda_last_error());

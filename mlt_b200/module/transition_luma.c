@@ -68,6 +68,7 @@ static mlt_producer refresh_map(mlt_transition self, mlt_frame a_frame, uint16_t
         mlt_properties_set_int(props, "width", *lw);
         mlt_properties_set_int(props, "height", *lh);
         mlt_properties_set(props, "_resource", named);
+        mlt_properties_set_int(props, CUDA_MAP_GENERATION, mlt_properties_get_int(props, CUDA_MAP_GENERATION) + 1);
         mlt_properties_set_data(props, "bitmap", *bitmap, *lw * *lh * 2, mlt_pool_release, NULL);
         mlt_properties_clear(props, "producer");
         return NULL;
@@ -75,6 +76,7 @@ static mlt_producer refresh_map(mlt_transition self, mlt_frame a_frame, uint16_t
     if (!*resource) {
         *bitmap = NULL;
         mlt_properties_set(props, "_resource", NULL);
+        mlt_properties_set_int(props, CUDA_MAP_GENERATION, mlt_properties_get_int(props, CUDA_MAP_GENERATION) + 1);
         mlt_properties_set_data(props, "bitmap", NULL, 0, mlt_pool_release, NULL);
         mlt_properties_clear(props, "producer");
         return NULL;
@@ -110,6 +112,7 @@ static mlt_producer refresh_map(mlt_transition self, mlt_frame a_frame, uint16_t
         }
         mlt_properties_set_int(props, "width", *lw);
         mlt_properties_set_int(props, "height", *lh);
+        mlt_properties_set_int(props, CUDA_MAP_GENERATION, mlt_properties_get_int(props, CUDA_MAP_GENERATION) + 1);
         mlt_properties_set_data(props, "bitmap", *bitmap, *lw * *lh * 2, mlt_pool_release, NULL);
         mlt_frame_close(lf);
     }
@@ -230,7 +233,7 @@ static int luma_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_image_for
         /* launches go to the context that owns the destination's buffers */
         mltcuda_ctx *ctx = dst->ctx;
         rc = cuda_image_localize(src, ctx);
-        if (!rc && have_map && !(d.map = cuda_cached_map(props, "luma.map", ctx, bitmap, lw, lh)))
+        if (!rc && have_map && !(d.map = cuda_cached_map(props, "luma.map", ctx, bitmap, lw, lh, mlt_properties_get_int(props, CUDA_MAP_GENERATION))))
             rc = 1;
         d.format = work;
         d.width = *width, d.height = *height;

@@ -37,6 +37,21 @@ def test_module_registers_reference_names_and_aliases(tmp_path):
     assert "(CUDA)" in melt_query(tmp_path, "transition=cuda.affine")
 
 
+def test_metadata_lists_every_parameter_of_the_reference_services(tmp_path):
+    """melt -query of the CUDA services shows at least the parameters the stock services document (SURVEY 8(b):
+    same property names), parsed from the stock YAML shipped with the reference build."""
+    import yaml
+    for kind, name, mod in (("transition", "composite", "core"), ("transition", "luma", "core"), ("transition", "affine", "plus")):
+        ref = yaml.safe_load(open(os.path.join(mltenv.REF, "share", "mlt", mod, f"{kind}_{name}.yml")))
+        ours = yaml.safe_load(melt_query(tmp_path, f"{kind}={name}").replace("...", ""))
+        assert "(CUDA)" in ours["title"]
+        want = {p["identifier"] for p in ref.get("parameters", [])}
+        have = {p["identifier"] for p in ours.get("parameters", [])}
+        assert want <= have, f"{name}: missing {sorted(want - have)}"
+        for p in ours["parameters"]:
+            assert p.get("title") and (p.get("type") or p["identifier"].endswith(".*")), p
+
+
 def test_module_exports_mlt_register():
     out = subprocess.check_output(["nm", "-D", "--defined-only", mltenv.MODULE]).decode()
     assert " T mlt_register" in out
