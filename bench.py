@@ -527,7 +527,7 @@ def run_ours(args, dist):
     e2e = None
     threads = args.melt_threads or max(2, min(8, (os.cpu_count() or 8) // max(1, dist.world)))
     e2e_resident = None
-    if have_reference() and meltenv.have_module():
+    if have_reference() and meltenv.have_module() and not args.no_melt:
         base = tempfile.mkdtemp(prefix=f"mltbench_{dist.rank}_")
         ex = {"MLT_CUDA_DEVICE": str(dev), "MLT_CUDA_STATS": "1"}
         r = melt_steady(args.melt_frames, args.melt_warm, threads, True, base, dist=dist, extra=ex)
@@ -667,6 +667,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the 1080p cfg1..cfg4 device legs")
     ap.add_argument("--no-e2e-abi", action="store_true", help="skip the C-ABI-only end-to-end leg")
+    ap.add_argument("--no-melt", action="store_true", help="skip the melt + module legs (profiler runs: the device legs only)")
     ap.add_argument("--streams", type=int, default=2, help="worker contexts (streams) per GPU on the device leg, 1..8")
     ap.add_argument("--melt-threads", type=int, default=0, help="real_time=-T of the melt + module leg (0 = auto)")
     ap.add_argument("--melt-warm", type=int, default=1024, help="frames of the melt + module run before its timed window")

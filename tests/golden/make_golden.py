@@ -13,6 +13,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 import mltenv  # noqa: E402
 import refmlt  # noqa: E402
 
@@ -62,6 +63,9 @@ FRAMES = {
     "cfg3_affine_yuv422": ("yuv422", 100, ["noise:", "out=249", "-track", "noise:", "out=249", "meta.media.width=1920", "meta.media.height=1080", "-attach", "mirror:flip", "-transition", "affine", "rect=0=10%/10%:50%x50%:100%; 249=30%/30%:70%x70%:60%", "rotate_x=1", "in=0", "out=249", "a_track=0", "b_track=1"]),
     "cfg4_1080p_f0": ("yuv422", 0, None),
     "cfg4_1080p_f37": ("yuv422", 37, None),
+    # the full BASELINE size: cfg4 on uhd_2160p_60 (4th tuple element = profile)
+    "cfg4_2160p_f300": ("yuv422", 300, None, "uhd_2160p_60"),
+    "cfg4_2160p_f599": ("yuv422", 599, None, "uhd_2160p_60"),
 }
 CFG4 = ["noise:", "out=599", "-track", "noise:", "out=599", "-attach", "mirror:flip", "-transition", "composite", "a_track=0", "b_track=1", "geometry=5%/5%:40%x40%:80%", "-track", "colour:0x3060c0a0", "out=599", "-transition", "affine", "a_track=0", "b_track=2", "rect=0=20%/20%:50%x50%:90%; 599=30%/25%:60%x60%:70%", "rotate_x=0.5", "-track", "noise:", "out=599", "-transition", "composite", "a_track=0", "b_track=3", "geometry=55%/55%:40%x40%:100%"]
 
@@ -91,11 +95,13 @@ def main():
 
     hashes = {}
     td = tempfile.mkdtemp()
-    for name, (fmt, frame, args) in FRAMES.items():
+    for name, spec in FRAMES.items():
+        fmt, frame, args = spec[:3]
+        profile = spec[3] if len(spec) > 3 else "atsc_1080p_25"
         args = args or CFG4
-        out = subprocess.check_output([mltenv.DUMP, "atsc_1080p_25", fmt, os.path.join(td, "g"), str(frame), "--"] + args,
+        out = subprocess.check_output([mltenv.DUMP, profile, fmt, os.path.join(td, "g"), str(frame), "--"] + args,
                                       env=mltenv.env(), stderr=subprocess.DEVNULL).decode().split()
-        hashes[name] = {"profile": "atsc_1080p_25", "format": fmt, "frame": frame, "width": int(out[1]),
+        hashes[name] = {"profile": profile, "format": fmt, "frame": frame, "width": int(out[1]),
                         "height": int(out[2]), "image_fnv1a64": out[4], "alpha_fnv1a64": out[5],
                         "args": [a.replace(mltenv.LUMA_PGM, "@LUMA1_PGM@") for a in args]}
     json.dump({"seed": SEED, "reference": "MLT 7.41.0, oracle/Makefile.ref Release flags, x86-64", "frames": hashes},

@@ -95,3 +95,14 @@ def test_gpu_fused_tractor_reproduces_golden_cfg4_hashes(ctx):
         fus = pipeline.gpu_fused(ctx, pipeline.inputs(frame, W, H))
         assert fnv1a64(fus["out"]) == FRAMES[key]["image_fnv1a64"], key
         assert fnv1a64(fus["alpha"]) == FRAMES[key]["alpha_fnv1a64"], key
+
+
+@pytest.mark.gpu
+def test_gpu_fused_tractor_reproduces_golden_cfg4_hashes_at_2160p(ctx):
+    """The full BASELINE size: frames the compiled reference rendered on uhd_2160p_60 (tests/golden/frames.json)."""
+    W, H = 3840, 2160
+    for frame, key in ((300, "cfg4_2160p_f300"), (599, "cfg4_2160p_f599")):
+        assert FRAMES[key]["width"] == W and FRAMES[key]["height"] == H
+        fus = pipeline.gpu_fused(ctx, pipeline.inputs(frame, W, H))
+        assert fnv1a64(fus["out"]) == FRAMES[key]["image_fnv1a64"], key
+        assert fnv1a64(fus["alpha"]) == FRAMES[key]["alpha_fnv1a64"], key

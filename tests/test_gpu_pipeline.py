@@ -19,11 +19,10 @@ def test_cfg4_fused_unfused_oracle(ctx, W, H, frame):
     # fused and unfused run identical device arithmetic: byte-identical
     assert np.array_equal(fus["out"], unf["out"])
     assert np.array_equal(fus["alpha"], unf["alpha"])
-    # vs the oracle: integer stages exact, the float affine +-1 LSB in rgba -> at most 2 after rgb->yuv
-    diff = np.abs(fus["out"].astype(int) - exp["out"].astype(int))
-    assert diff.max() <= 2
-    assert (diff > 0).mean() < 0.01
-    assert np.abs(fus["alpha"].astype(int) - exp["alpha"].astype(int)).max() <= 1
+    # vs the oracle (pinned to the compiled reference by tests/test_golden.py): the kernels follow the Release
+    # build's operation order, so the whole chain is byte-identical, float affine included
+    assert np.array_equal(fus["out"], exp["out"])
+    assert np.array_equal(fus["alpha"], exp["alpha"])
 
 
 def test_cfg4_uhd_properties(ctx):
