@@ -659,6 +659,7 @@ def e2e_abi_leg(lib, dist, workers, S, steps, dev):
 
 
 def main():
+    global REPEAT, FRAMES_PER_STEP
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -672,7 +673,10 @@ def main():
     ap.add_argument("--melt-threads", type=int, default=0, help="real_time=-T of the melt + module leg (0 = auto)")
     ap.add_argument("--melt-warm", type=int, default=1024, help="frames of the melt + module run before its timed window")
     ap.add_argument("--melt-frames", type=int, default=12000, help="frames of the melt + module run")
+    ap.add_argument("--repeat", type=int, default=REPEAT, help="walks over the 32 distinct frames per step (profiler runs use 1)")
     args = ap.parse_args()
+    REPEAT, FRAMES_PER_STEP = max(1, args.repeat), DISTINCT * max(1, args.repeat)
+    CONFIG["frames_per_step"] = FRAMES_PER_STEP
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     dist = Dist()
     try:

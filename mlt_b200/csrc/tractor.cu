@@ -8,6 +8,7 @@
 // the group is pair-aligned, so all intermediate integer steps -- chroma pair averaging, clamps,
 // alpha-plane creation -- are reproduced exactly: the output is byte-identical to running the ops
 // as separate launches.  HBM traffic: A read once + written once + each layer's pixels once.
+#include <stdlib.h>
 #include "common.cuh"
 #include "pixel_ops.cuh"
 
@@ -90,8 +91,11 @@ __host__ __device__ constexpr int sig_first(uint32_t sig, uint32_t code)
 #ifndef K5_MINB
 #define K5_MINB 8
 #endif
+#ifndef K5_GEN_MINB
+#define K5_GEN_MINB 8
+#endif
 template <bool ONLY_BL, uint32_t SIG>
-__global__ void __launch_bounds__(128, ONLY_BL ? K5_MINB : 2) k_tractor(const __grid_constant__ TractorK K)
+__global__ void __launch_bounds__(128, ONLY_BL ? (SIG ? K5_MINB : K5_GEN_MINB) : 2) k_tractor(const __grid_constant__ TractorK K)
 {
     // 2-D CTA: 32 groups (256 px) x 4 rows (128-thread CTAs balance the heavy affine tiles better than 256: +2.8%) -- no div/mod, and the B taps of neighbouring rows share L1
     const int c = blockIdx.x * 32 + threadIdx.x;
@@ -449,12 +453,24 @@ extern "C" int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d)
     case S: \
         k_tractor<true, S><<<grd, blk, 0, ctx->stream>>>(K); \
         break;
-    switch (only_bl ? sig : 0xffffffffu) {
+    // MLTCUDA_TRACTOR_GENERIC=1: always the run-time-interpreted instantiation (what an unlisted graph shape gets);
+    // used by tools/ktractor.py to time it against the specialised ones
+    static const bool force_generic = [] {
+        const char *e = getenv("MLTCUDA_TRACTOR_GENERIC");
+        return e && *e && *e != '0';
+    }();
+    switch (only_bl && !force_generic ? sig : 0xffffffffu) {
         MC_TRACTOR_SIG(0x1)     // composite
         MC_TRACTOR_SIG(0x11)    // composite x2
         MC_TRACTOR_SIG(0x111)   // composite x3
         MC_TRACTOR_SIG(0x3)     // luma wipe
+        MC_TRACTOR_SIG(0x1111)  // composite x4
+        MC_TRACTOR_SIG(0x13)    // luma wipe, composite (a wipe between two clips under an overlay)
+        MC_TRACTOR_SIG(0x31)    // composite, luma wipe
+        MC_TRACTOR_SIG(0x24)    // ->rgba, affine (rgba consumer: cfg3)
         MC_TRACTOR_SIG(0x524)   // ->rgba, affine, ->yuv422
+        MC_TRACTOR_SIG(0x5241)  // composite, ->rgba, affine, ->yuv422
+        MC_TRACTOR_SIG(0x1524)  // ->rgba, affine, ->yuv422, composite
         MC_TRACTOR_SIG(0x15241) // cfg4: composite, ->rgba, affine, ->yuv422, composite
     default:
         if (only_bl)

@@ -32,9 +32,13 @@ if __name__ == "__main__":
     ap.add_argument("--h", type=int, default=2160)
     ap.add_argument("--distinct", type=int, default=32)
     ap.add_argument("--repeat", type=int, default=8)
+    ap.add_argument("--interp", default="bilinear", help="affine sampler: nearest | bilinear | bicubic (non-bilinear = the ONLY_BL=false instantiation)")
     a = ap.parse_args()
     lib = abi.load()
     workers = [Context(0) for _ in range(a.streams)]
+    if a.interp != "bilinear":
+        _ap = workloads.affine_params
+        workloads.affine_params = lambda *x, **k: _ap(*x[:7], a.interp)
     S = bench.cfg4_setup(lib, workers[0], 0, a.distinct, a.w, a.h)
     full, fused_only = bench.cfg4_steps(lib, S, workers, a.repeat)
     timed = bench.Timed(lib, workers)
@@ -44,5 +48,5 @@ if __name__ == "__main__":
     alg = float(np.mean([a.w * a.h * 5 + S["b1b"] + S["b3b"] + 4 * c for c in cov]))
     us = ms * 1e3 / launches
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0)
-    print(f"k_tractor {a.w}x{a.h}: {launches} launches, {us:.2f} us/launch, {1e6 / us:.0f} frames/s, "
+    print(f"k_tractor {a.w}x{a.h} {a.interp}{' generic' if os.environ.get('MLTCUDA_TRACTOR_GENERIC') else ''}: {launches} launches, {us:.2f} us/launch, {1e6 / us:.0f} frames/s, "
           f"{alg / us / 1e3:.1f} GB/s algorithmic = {alg / us / 1e3 / peak:.4f} of measured {peak} GB/s")
