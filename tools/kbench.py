@@ -201,10 +201,11 @@ def main():
 
     # K6 producers
     run("K6 noise yuv422", lambda: abi.check(lib.mltcuda_noise(ctx.h, d_y1.ptr, W, H, 7, B, yb)), B * NPX * 2)
-    d_half = ctx.alloc((W // 2) * (H // 2) * 2)
+    hb = (W // 2) * (H // 2) * 2
+    d_half = ctx.alloc(B * hb)
     run("K6 rescale_nn yuv422 2160p->1080p",
-        lambda: abi.check(lib.mltcuda_rescale_yuv422(ctx.h, d_half.ptr, W // 2, H // 2, d_y0.ptr, W, H, 1, 0, 0)),
-        (W // 2) * (H // 2) * 4, "single frame (no batch axis): L2-resident, launch-bound")
+        lambda: abi.check(lib.mltcuda_rescale_yuv422(ctx.h, d_half.ptr, W // 2, H // 2, d_y0.ptr, W, H, B, hb, yb)),
+        B * (W // 2) * (H // 2) * 4, "2 B/px written + 2 B/px sampled (every other pixel of every other row)")
     if args.out:
         with open(args.out, "w") as f:
             for ln in lines:
