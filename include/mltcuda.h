@@ -323,6 +323,11 @@ int mltcuda_rescale_alpha(mltcuda_ctx *ctx, uint8_t *dst, int dst_w, int dst_h,
 int mltcuda_resize_pad(mltcuda_ctx *ctx, void *dst, int dst_w, int dst_h, const void *src, int src_w,
                        int src_h, int format, int alpha_value);
 
+/* Horizontal mirror of core `mirror` in its "flip" mode (src/modules/core/filter_mirror.c:247-294): rows reversed
+ * pair-wise (Y1 U Y0 V), alpha plane reversed.  Out of place; even widths (MLTCUDA_E_UNSUPPORTED otherwise). */
+int mltcuda_mirror_flip(mltcuda_ctx *ctx, uint8_t *dst_yuv422, uint8_t *dst_alpha, const uint8_t *src_yuv422,
+                        const uint8_t *src_alpha, int width, int height);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

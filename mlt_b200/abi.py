@@ -126,6 +126,7 @@ SIGNATURES = {
     "mltcuda_colour": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_uint8, C.c_uint8, C.c_uint8, C.c_uint8]),
     "mltcuda_rescale_yuv422": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int, sz, sz]),
     "mltcuda_rescale_alpha": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, C.c_int, C.c_int]),
+    "mltcuda_mirror_flip": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int]),
     "mltcuda_resize_pad": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int]),
 }
 

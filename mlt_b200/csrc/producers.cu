@@ -225,6 +225,32 @@ __global__ void __launch_bounds__(256) k_resize_pad(uint8_t *dst, int orow, int 
     }
 }
 
+// mirror:flip (src/modules/core/filter_mirror.c:247-281): every row reversed pair-wise; inside a pair the two
+// lumas swap and the shared chroma stays (output pair k = input pair n-1-k as Y1 U Y0 V).  One thread = VEC pairs.
+template <int VEC> __global__ void __launch_bounds__(256) k_mirror_flip_yuv422(uint8_t *dst, const uint8_t *src, int npairs)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x; // group of VEC output pairs
+    if (g * VEC >= npairs)
+        return;
+    const size_t row = (size_t) blockIdx.y * npairs * 4;
+    const uint32_t *in = reinterpret_cast<const uint32_t *>(src + row);
+    uint32_t *out = reinterpret_cast<uint32_t *>(dst + row);
+    if (VEC == 4) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4 *>(in + (npairs - 4 - 4 * g)));
+        *reinterpret_cast<uint4 *>(out + 4 * g) = make_uint4(__byte_perm(v.w, 0, 0x3012), __byte_perm(v.z, 0, 0x3012),
+                                                             __byte_perm(v.y, 0, 0x3012), __byte_perm(v.x, 0, 0x3012));
+    } else {
+        out[g] = __byte_perm(__ldg(in + (npairs - 1 - g)), 0, 0x3012);
+    }
+}
+// the alpha plane of the same filter (:283-294): every row reversed
+__global__ void __launch_bounds__(256) k_mirror_flip_plane(uint8_t *dst, const uint8_t *src, int w)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < w)
+        dst[(size_t) blockIdx.y * w + j] = __ldg(src + (size_t) blockIdx.y * w + (w - 1 - j));
+}
+
 int ensure_noise_tab(mltcuda_ctx *ctx)
 {
     if (ctx->noise_tab)
@@ -395,4 +421,28 @@ extern "C" int mltcuda_resize_pad(mltcuda_ctx *ctx, void *dst, int ow, int oh, c
     k_resize_pad<<<grd, 256, 0, ctx->stream>>>((uint8_t *) dst, ow * bpp, oh, (const uint8_t *) src, iw * bpp, ih, off_x, off_y,
                                                pattern);
     return mc_after_launch(ctx, "k_resize_pad");
+}
+
+extern "C" int mltcuda_mirror_flip(mltcuda_ctx *ctx, uint8_t *dst, uint8_t *dst_alpha, const uint8_t *src, const uint8_t *src_alpha,
+                                   int width, int height)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!dst || !src || dst == src || width <= 0 || height <= 0 || height > 65535, "bad argument");
+    if (width % 2) {
+        mltcuda_set_error("mirror flip: odd width %d (the reference's odd-width byte shuffle is not reproduced on the device)", width);
+        return MLTCUDA_E_UNSUPPORTED;
+    }
+    const int npairs = width / 2;
+    if (npairs % 4 == 0 && (((uintptr_t) dst | (uintptr_t) src) & 15) == 0)
+        k_mirror_flip_yuv422<4><<<dim3(mc_blocks(npairs / 4, 256), height, 1), 256, 0, ctx->stream>>>(dst, src, npairs);
+    else
+        k_mirror_flip_yuv422<1><<<dim3(mc_blocks(npairs, 256), height, 1), 256, 0, ctx->stream>>>(dst, src, npairs);
+    if (int e = mc_after_launch(ctx, "k_mirror_flip_yuv422"))
+        return e;
+    if (src_alpha && dst_alpha) {
+        k_mirror_flip_plane<<<dim3(mc_blocks(width, 256), height, 1), 256, 0, ctx->stream>>>(dst_alpha, src_alpha, width);
+        return mc_after_launch(ctx, "k_mirror_flip_plane");
+    }
+    return 0;
 }

@@ -89,7 +89,7 @@ static const char *g_stat_name[CS_N] = {"composite get_image (incl. inputs)", "l
                                         "upload", "cuda_frame_get_image (pull input)", "worker context creation", "pinned host buffer (pool)",
                                         "fused pass (k_tractor launches)", "ops fused into k_tractor", "unfused composite launches",
                                         "unfused affine launches", "unfused luma launches", "unfused convert launches",
-                                        "rescale launches", "resize pad launches"};
+                                        "rescale launches", "resize pad launches", "mirror flip launches"};
 uint64_t cuda_stat_now(void)
 {
     struct timespec ts;

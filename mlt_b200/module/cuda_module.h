@@ -68,7 +68,7 @@ mltcuda_ctx *cuda_thread_ctx(void);
 /* MLT_CUDA_STATS=1: wall time per stage, summed over the worker threads, printed at exit (stderr).
  * Inclusive times: a transition's figure contains the get_image of its inputs. */
 enum { CS_COMPOSITE, CS_LUMA, CS_AFFINE, CS_CONVERT, CS_NOISE, CS_COLOUR, CS_DOWNLOAD, CS_UPLOAD, CS_PULL_A, CS_CTX_CREATE, CS_HOSTPOOL,
-       CS_FUSED, CS_FUSED_OPS, CS_K_COMPOSITE, CS_K_AFFINE, CS_K_LUMA, CS_K_CONVERT, CS_K_RESCALE, CS_K_PAD, CS_N };
+       CS_FUSED, CS_FUSED_OPS, CS_K_COMPOSITE, CS_K_AFFINE, CS_K_LUMA, CS_K_CONVERT, CS_K_RESCALE, CS_K_PAD, CS_K_MIRROR, CS_N };
 /* count-only entries (no time): */
 void cuda_stat_count(int id, uint64_t n);
 void cuda_stat_bytes(int id, uint64_t n);
@@ -147,6 +147,7 @@ int cuda_convert_image(mlt_frame frame, uint8_t **image, mlt_image_format *forma
 /* filter_rescale.c: the loader's stock `rescale` / `resize` normalisers answer CUDA requests on the device */
 void cuda_rescale_install(mlt_filter stock_rescale);
 void cuda_resize_install(mlt_filter stock_resize);
+void cuda_mirror_install(mlt_filter stock_mirror); /* mirror:flip between a device producer and a CUDA transition */
 /* cuda_image.c: registers the imageconvert filter's converter on a frame (appended, like the reference) */
 void cuda_imageconvert_attach(mlt_frame frame);
 /* true if a device producer may answer this request with a resident image */

@@ -115,6 +115,13 @@ static void on_producer_done(mlt_properties owner, void *unused, mlt_event_data 
     }
 }
 
+/* MLT_CUDA_MIRROR=0 leaves core `mirror` on the host (a device producer's frame is then downloaded for it) */
+static int mirror_enabled(void)
+{
+    const char *e = getenv("MLT_CUDA_MIRROR");
+    return !(e && (!strcmp(e, "0") || !strcmp(e, "off") || !strcmp(e, "no")));
+}
+
 /* the loader's stock `rescale` / `resize` normalisers get their device paths (filter_rescale.c) */
 static void on_filter_done(mlt_properties owner, void *unused, mlt_event_data ev)
 {
@@ -125,6 +132,8 @@ static void on_filter_done(mlt_properties owner, void *unused, mlt_event_data ev
         cuda_rescale_install(*(mlt_filter *) d->service);
     if (!strcmp(d->name, "resize"))
         cuda_resize_install(*(mlt_filter *) d->service);
+    if (!strcmp(d->name, "mirror") && mirror_enabled())
+        cuda_mirror_install(*(mlt_filter *) d->service);
 }
 
 static mlt_properties metadata(mlt_service_type type, const char *id, void *data)

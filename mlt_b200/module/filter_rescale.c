@@ -215,11 +215,48 @@ static mlt_frame resize_process(mlt_filter filter, mlt_frame frame)
     return wrap_process(filter, frame, resize_get_image, 1);
 }
 
+/* ---- mirror (flip) ----------------------------------------------------------------------------------- */
+
+/* core `mirror` (src/modules/core/filter_mirror.c) works in place on a host yuv422 picture: between a device
+ * producer and a CUDA transition it costs a download, the CPU shuffle and an upload per frame (the track-1
+ * decorrelator of the benchmark graphs).  Its "flip" mode on an even-width picture is done on the
+ * device when a CUDA service is pulling; every other mode, odd widths and every host request stay with the
+ * stock code. */
+static int mirror_get_image(mlt_frame frame, uint8_t **image, mlt_image_format *format, int *width, int *height, int writable)
+{
+    mlt_filter filter = mlt_frame_pop_service(frame);
+    const int pushed = mlt_frame_pop_service_int(frame);
+    const char *mode = mlt_properties_get(MLT_FILTER_PROPERTIES(filter), "mirror");
+    if (!is_cuda_request(frame, *format) || !mode || strcmp(mode, "flip") || *width % 2)
+        return mlt_frame_get_image(frame, image, format, width, height, writable); /* the stock mirror */
+    discard_stock_entries(frame, pushed);
+    cuda_image ci = cuda_frame_get_image(frame, mlt_image_yuv422, width, height, 1); /* the filter works in yuv422 (:300) */
+    if (!ci)
+        return 1;
+    CUDA_STAT_COUNT(CS_K_MIRROR, 1);
+    cuda_image out = cuda_image_new(ci->ctx, mlt_image_yuv422, ci->width, ci->height, ci->alpha != NULL);
+    if (!out || mltcuda_mirror_flip(ci->ctx, out->data, out->alpha, ci->data, ci->alpha, ci->width, ci->height)
+        || cuda_frame_set_image(frame, out)) {
+        mlt_log_error(MLT_FILTER_SERVICE(filter), "[cuda] mirror flip %dx%d failed: %s\n", ci->width, ci->height, mltcuda_last_error());
+        cuda_image_close(out);
+        return 1;
+    }
+    ci = out;
+    *width = ci->width, *height = ci->height;
+    *image = (uint8_t *) ci, *format = mlt_image_private;
+    return 0;
+}
+
+static mlt_frame mirror_process(mlt_filter filter, mlt_frame frame)
+{
+    return wrap_process(filter, frame, mirror_get_image, 0);
+}
+
 /* ---- installation (factory.c: "filter-create-done") ------------------------------------------------- */
 
 static void install(mlt_filter f, process_fn ours)
 {
-    if (!f || !f->process || f->process == rescale_process || f->process == resize_process)
+    if (!f || !f->process || f->process == rescale_process || f->process == resize_process || f->process == mirror_process)
         return;
     mlt_properties_set_data(MLT_FILTER_PROPERTIES(f), "_cuda_stock_process", (void *) f->process, 0, NULL, NULL);
     f->process = ours;
@@ -233,4 +270,9 @@ void cuda_rescale_install(mlt_filter stock_rescale)
 void cuda_resize_install(mlt_filter stock_resize)
 {
     install(stock_resize, resize_process);
+}
+
+void cuda_mirror_install(mlt_filter stock_mirror)
+{
+    install(stock_mirror, mirror_process);
 }

@@ -413,3 +413,20 @@ def test_rescale(ctx, iw, ih, ow, oh):
     d_src, d_dst = ctx.put(src), ctx.put(init)
     abi.check(ctx.lib.mltcuda_rescale_yuv422(ctx.h, d_dst.ptr, ow, oh, d_src.ptr, iw, ih, 1, 0, 0))
     assert np.array_equal(ctx.get(d_dst, exp.shape), exp)
+
+
+@pytest.mark.parametrize("w,h,alpha", [(1920, 1080, False), (1536, 864, True), (642, 37, True), (2, 3, False), (10, 5, True)])
+def test_mirror_flip(ctx, w, h, alpha):
+    """core mirror:flip (filter_mirror.c:247-294): rows reversed pair-wise with the lumas of a pair swapped."""
+    rng = np.random.default_rng(w * 31 + h)
+    src = rng.integers(0, 256, w * h * 2).astype(np.uint8)
+    al = rng.integers(0, 256, w * h).astype(np.uint8) if alpha else None
+    exp = np.ascontiguousarray(src.reshape(h, w // 2, 4)[:, ::-1, :][:, :, [2, 1, 0, 3]]).reshape(-1)
+    d_src, d_dst = ctx.put(src), ctx.alloc(w * h * 2)
+    d_al = ctx.put(al) if alpha else None
+    d_alo = ctx.alloc(w * h) if alpha else None
+    abi.check(ctx.lib.mltcuda_mirror_flip(ctx.h, d_dst.ptr, d_alo.ptr if alpha else None, d_src.ptr, d_al.ptr if alpha else None, w, h))
+    assert np.array_equal(ctx.get(d_dst, (w * h * 2,)), exp)
+    if alpha:
+        assert np.array_equal(ctx.get(d_alo, (w * h,)), np.ascontiguousarray(al.reshape(h, w)[:, ::-1]).reshape(-1))
+    assert ctx.lib.mltcuda_mirror_flip(ctx.h, d_dst.ptr, None, d_src.ptr, None, 7, 4) == abi.E_UNSUPPORTED
