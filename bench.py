@@ -9,8 +9,8 @@ consecutive frames, each with its own keyframed parameters and its own buffers (
 >> the 126 MB L2, so no L2 flush), walked 16 times.
 
 ours arm, one JSON line:
-  value     device leg through the C-ABI, per frame: the three device noise producers (k_noise) + ONE
-            fused launch (mltcuda_tractor), round-robin over two worker contexts (= two of MLT's
+  value     device leg through the C-ABI, per frame: the three device noise producers (k_noise), track 1's
+            mirror:flip (k_mirror_flip) + ONE fused launch (mltcuda_tractor), round-robin over two worker contexts (= two of MLT's
             real_time worker threads); CUDA events on the launching stream, max over ranks.
   roofline  the fused kernel alone (second timed region, same frames): algorithmic bytes per launch
             / average launch time vs MEASURED_PEAKS.json.
@@ -324,6 +324,7 @@ def cfg4_setup(lib, ctx, first, F, w, h):
     fb, b1b, b3b = w * h * 2, b1w * b1h * 2, b2w * b2h * 2
     S = dict(frames=frames, fb=fb, b1b=b1b, b3b=b3b, b1=(b1w, b1h), b3=(b2w, b2h), first=first, F=F, w=w, h=h)
     S["d_in"], S["d_b1"], S["d_b3"] = ctx.alloc(F * fb), ctx.alloc(F * b1b), ctx.alloc(F * b3b)
+    S["d_b1raw"] = ctx.alloc(F * b1b)  # track 1 before its mirror:flip
     S["d_bc"], d_bcy, d_bca = ctx.alloc(w * h * 4), ctx.alloc(fb), ctx.alloc(w * h)
     S["d_out"], S["d_alpha"] = ctx.alloc(F * fb), ctx.alloc(F * w * h)
     # colour B of the affine: the producer's yuv422 + alpha plane converted to rgba, as the normaliser chain does
@@ -344,13 +345,14 @@ def cfg4_steps(lib, S, workers, repeat):
     nw = len(workers)
 
     def produce(i, c):
-        # track 0 and track 3: the noise producer at the frame's position; track 1: the same producer re-seeded
-        # (stands in for noise + the CPU filter mirror:flip, which is not part of the path)
+        # the graph's producers and its track-1 filter: noise at the frame's position on tracks 0, 1 and 3
+        # (producer_noise.c), mirror:flip on track 1 (filter_mirror.c) -- all on the device, as the module runs them
         rc = lib.mltcuda_noise(c.h, S["d_in"].at(i * fb), w, h, first + i, 1, 0)
-        rc |= lib.mltcuda_noise(c.h, S["d_b1"].at(i * b1b), b1w, b1h, first + i + 100000, 1, 0)
+        rc |= lib.mltcuda_noise(c.h, S["d_b1raw"].at(i * b1b), b1w, b1h, first + i, 1, 0)
+        rc |= lib.mltcuda_mirror_flip(c.h, S["d_b1"].at(i * b1b), None, S["d_b1raw"].at(i * b1b), None, b1w, b1h)
         rc |= lib.mltcuda_noise(c.h, S["d_b3"].at(i * b3b), b3w, b3h, first + i, 1, 0)
         if rc:
-            abi.check(rc, "mltcuda_noise")
+            abi.check(rc, "producers")
 
     def full():
         for _ in range(repeat):
@@ -573,9 +575,8 @@ def run_ours(args, dist):
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_max / args.steps, 4),
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
                 "config": dict(CONFIG),
-                "arm": {"timed_region": "per frame 3 k_noise (tracks 0, 1, 3) + 1 k_tractor; track 1 = re-seeded device noise "
-                                        "(the CPU filter mirror:flip of the melt graph is not on the path and is excluded); "
-                                        "colour track resident (constant)",
+                "arm": {"timed_region": "per frame 3 k_noise (tracks 0, 1, 3) + k_mirror_flip (track 1) + 1 k_tractor = the melt graph's "
+                                        "device work; colour track resident (constant)",
                         "launches_per_frame": round(total_launches / (dist.world * FRAMES_PER_STEP * args.steps), 3),
                         "worker_streams": len(workers), "parallelism": f"frame-sharded x{dist.world}, no collective"},
                 "e2e": e2e, "gpu_launches": total_launches, "roofline": roofline, "clocks": clk}

@@ -206,6 +206,9 @@ def main():
     run("K6 rescale_nn yuv422 2160p->1080p",
         lambda: abi.check(lib.mltcuda_rescale_yuv422(ctx.h, d_half.ptr, W // 2, H // 2, d_y0.ptr, W, H, B, hb, yb)),
         B * (W // 2) * (H // 2) * 4, "2 B/px written + 2 B/px sampled (every other pixel of every other row)")
+    run("K6 mirror flip yuv422 (16 frames, one launch each)",
+        lambda: [abi.check(lib.mltcuda_mirror_flip(ctx.h, d_y1.ptr + i * yb, None, d_y0.ptr + i * yb, None, W, H)) for i in range(B)],
+        B * NPX * 4)
     if args.out:
         with open(args.out, "w") as f:
             for ln in lines:
