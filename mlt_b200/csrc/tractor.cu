@@ -61,7 +61,7 @@ struct TractorK
     TOp ops[MLTCUDA_TRACTOR_MAX_OPS];
 };
 
-// ONLY_BL: every affine op of the list samples bilinearly (the default "consumer.rescale"), so the
+// MODE 1 (ONLY_BL): every affine op of the list samples bilinearly (the default "consumer.rescale"), so the
 // nearest / bicubic samplers are compiled out -- they would otherwise set the register budget.
 //
 // SIG: 0 = interpret the op list at run time.  Otherwise the op list itself, 4 bits per slot
@@ -94,9 +94,12 @@ __host__ __device__ constexpr int sig_first(uint32_t sig, uint32_t code)
 #ifndef K5_GEN_MINB
 #define K5_GEN_MINB 8
 #endif
-template <bool ONLY_BL, uint32_t SIG>
-__global__ void __launch_bounds__(128, ONLY_BL ? (SIG ? K5_MINB : K5_GEN_MINB) : 2) k_tractor(const __grid_constant__ TractorK K)
+// MODE: 1 = every affine op samples bilinearly, 0 = every affine op samples nearest, 2 = anything else (sampler chosen
+// at run time).  Modes 0 and 1 compile exactly one sampler in and take the warp-transposed affine pass.
+template <int MODE, uint32_t SIG>
+__global__ void __launch_bounds__(128, MODE != 2 ? (SIG ? K5_MINB : K5_GEN_MINB) : 2) k_tractor(const __grid_constant__ TractorK K)
 {
+    constexpr bool ONLY_BL = MODE != 2; // "one sampler" (name kept from when bilinear was the only such mode)
     // 2-D CTA: 32 groups (256 px) x 4 rows (128-thread CTAs balance the heavy affine tiles better than 256: +2.8%) -- no div/mod, and the B taps of neighbouring rows share L1
     const int c = blockIdx.x * 32 + threadIdx.x;
     const int r = blockIdx.y * 4 + threadIdx.y;
@@ -228,20 +231,28 @@ __global__ void __launch_bounds__(128, ONLY_BL ? (SIG ? K5_MINB : K5_GEN_MINB) :
 #pragma unroll
                 for (int h4 = 0; h4 < 8; h4 += 4) {
                     BlTaps<uint8_t> taps[4];
+                    uint32_t ntap[4];
                     bool in[4];
 #pragma unroll
                     for (int k = 0; k < 4; k++) {
                         double dx, dy;
                         mc_affine_map_x(P, R, xl + (double) (32 * (h4 + k)), dx, dy);
                         in[k] = all || mc_affine_inside(P, dx, dy);
-                        if (in[k])
-                            taps[k] = mc_bl_fetch<uint8_t>(bimg, P.b_width, P.b_height, (float) dx, (float) dy);
+                        if (in[k]) {
+                            if (MODE == 1)
+                                taps[k] = mc_bl_fetch<uint8_t>(bimg, P.b_width, P.b_height, (float) dx, (float) dy);
+                            else
+                                ntap[k] = mc_nn_fetch<uint8_t>(bimg, P.b_width, (float) dx, (float) dy);
+                        }
                     }
 #pragma unroll
                     for (int k = 0; k < 4; k++)
                         if (in[k]) {
                             const int p = 32 * (h4 + k) + threadIdx.x;
-                            sm[p] = mc_bl_blend<uint8_t>(taps[k], P.mix, sm[p], P.b_alpha);
+                            if (MODE == 1)
+                                sm[p] = mc_bl_blend<uint8_t>(taps[k], P.mix, sm[p], P.b_alpha);
+                            else
+                                sm[p] = mc_nn_blend<uint8_t>(ntap[k], P.mix, sm[p], P.b_alpha);
                         }
                 }
                 __syncwarp();
@@ -260,7 +271,7 @@ __global__ void __launch_bounds__(128, ONLY_BL ? (SIG ? K5_MINB : K5_GEN_MINB) :
             const uint8_t *bimg = op.a.b_image + b * op.a.b_bs;
             asm volatile("" : "+l"(bimg)); // keep the batch base in registers
             // both end pixels inside B => the whole group is (monotone mapping): no per-pixel tests
-            if (ONLY_BL && mc_affine_inside(P, ax, ay) && mc_affine_inside(P, bx, by)) {
+            if (MODE == 1 && mc_affine_inside(P, ax, ay) && mc_affine_inside(P, bx, by)) {
                 // bilinear, whole group inside: taps of four pixels in flight before any blend
 #pragma unroll
                 for (int h4 = 0; h4 < 8; h4 += 4) {
@@ -278,7 +289,7 @@ __global__ void __launch_bounds__(128, ONLY_BL ? (SIG ? K5_MINB : K5_GEN_MINB) :
                     for (int k = 0; k < 4; k++)
                         rgba[h4 + k] = mc_bl_blend<uint8_t>(taps[k], P.mix, rgba[h4 + k], P.b_alpha);
                 }
-            } else if (!ONLY_BL && mc_affine_inside(P, ax, ay) && mc_affine_inside(P, bx, by)) {
+            } else if (MODE != 1 && mc_affine_inside(P, ax, ay) && mc_affine_inside(P, bx, by)) {
 #pragma unroll 1
                 for (int k = 0; k < 8; k++) {
                     double dx = ax, dy = ay;
@@ -286,8 +297,8 @@ __global__ void __launch_bounds__(128, ONLY_BL ? (SIG ? K5_MINB : K5_GEN_MINB) :
                         dx = bx, dy = by;
                     else if (k > 0)
                         mc_affine_map_x(P, R, x0 + (double) k, dx, dy);
-                    if (ONLY_BL)
-                        rgba[k] = mc_affine_sample_packed<uint8_t, 1>(P, bimg, dx, dy, rgba[k]);
+                    if (MODE != 2)
+                        rgba[k] = mc_affine_sample_packed<uint8_t, MODE == 1 ? 1 : 0>(P, bimg, dx, dy, rgba[k]);
                     else
                         rgba[k] = mc_affine_sample_packed_rt<uint8_t>(P, bimg, dx, dy, rgba[k]);
                 }
@@ -297,8 +308,8 @@ __global__ void __launch_bounds__(128, ONLY_BL ? (SIG ? K5_MINB : K5_GEN_MINB) :
                     double dx, dy;
                     mc_affine_map_x(P, R, x0 + (double) k, dx, dy);
                     if (mc_affine_inside(P, dx, dy)) {
-                        if (ONLY_BL)
-                            rgba[k] = mc_affine_sample_packed<uint8_t, 1>(P, bimg, dx, dy, rgba[k]);
+                        if (MODE != 2)
+                            rgba[k] = mc_affine_sample_packed<uint8_t, MODE == 1 ? 1 : 0>(P, bimg, dx, dy, rgba[k]);
                         else
                             rgba[k] = mc_affine_sample_packed_rt<uint8_t>(P, bimg, dx, dy, rgba[k]);
                     }
@@ -377,7 +388,7 @@ extern "C" int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d)
         MC_BADARG(!K.in_bs || !K.out_bs, "batch > 1 needs in/out bstride");
 
     int fmt = d->in_format, has_alpha = d->in_format == MLTCUDA_FMT_YUV422 && d->in_alpha != nullptr;
-    bool only_bl = true;
+    bool only_bl = true, only_nn = true;
     for (int i = 0; i < d->n_ops; i++) {
         const mltcuda_tractor_op &o = d->ops[i];
         TOp &t = K.ops[i];
@@ -418,6 +429,7 @@ extern "C" int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d)
             }
             t.a.b_image = (const uint8_t *) o.u.affine.b_image, t.a.b_bs = o.u.affine.b_bstride;
             only_bl = only_bl && t.a.ap.interp == MLTCUDA_INTERP_BL;
+            only_nn = only_nn && t.a.ap.interp == MLTCUDA_INTERP_NN;
         } else if (o.kind == MLTCUDA_TOP_LUMA) {
             const mltcuda_luma_desc &l = o.u.luma;
             MC_BADARG(fmt != MLTCUDA_FMT_YUV422 || l.format != MLTCUDA_FMT_YUV422 || !l.map || l.field_order >= 0,
@@ -442,41 +454,53 @@ extern "C" int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d)
     dim3 blk(32, 4, 1), grd((d->width / 8 + 31) / 32, (d->height + 4 - 1) / 4, K.batch);
     // op-list signature (see k_tractor): specialised instantiations for the common graph shapes
     uint32_t sig = 0;
-    if (only_bl && d->n_ops > 0) {
-        for (int i = d->n_ops - 1; i >= 0; i--) {
-            const mltcuda_tractor_op &o = d->ops[i];
-            uint32_t code = o.kind == MLTCUDA_TOP_CONVERT ? (o.to_format == MLTCUDA_FMT_RGBA ? 4u : 5u) : (uint32_t) o.kind;
-            sig = (sig << 4) | code;
-        }
+    bool has_affine = false;
+    for (int i = d->n_ops - 1; i >= 0; i--) {
+        const mltcuda_tractor_op &o = d->ops[i];
+        uint32_t code = o.kind == MLTCUDA_TOP_CONVERT ? (o.to_format == MLTCUDA_FMT_RGBA ? 4u : 5u) : (uint32_t) o.kind;
+        sig = (sig << 4) | code;
+        has_affine = has_affine || o.kind == MLTCUDA_TOP_AFFINE;
     }
-#define MC_TRACTOR_SIG(S) \
-    case S: \
-        k_tractor<true, S><<<grd, blk, 0, ctx->stream>>>(K); \
-        break;
     // MLTCUDA_TRACTOR_GENERIC=1: always the run-time-interpreted instantiation (what an unlisted graph shape gets);
     // used by tools/ktractor.py to time it against the specialised ones
     static const bool force_generic = [] {
         const char *e = getenv("MLTCUDA_TRACTOR_GENERIC");
         return e && *e && *e != '0';
     }();
-    switch (only_bl && !force_generic ? sig : 0xffffffffu) {
-        MC_TRACTOR_SIG(0x1)     // composite
-        MC_TRACTOR_SIG(0x11)    // composite x2
-        MC_TRACTOR_SIG(0x111)   // composite x3
-        MC_TRACTOR_SIG(0x3)     // luma wipe
-        MC_TRACTOR_SIG(0x1111)  // composite x4
-        MC_TRACTOR_SIG(0x13)    // luma wipe, composite (a wipe between two clips under an overlay)
-        MC_TRACTOR_SIG(0x31)    // composite, luma wipe
-        MC_TRACTOR_SIG(0x24)    // ->rgba, affine (rgba consumer: cfg3)
-        MC_TRACTOR_SIG(0x524)   // ->rgba, affine, ->yuv422
-        MC_TRACTOR_SIG(0x5241)  // composite, ->rgba, affine, ->yuv422
-        MC_TRACTOR_SIG(0x1524)  // ->rgba, affine, ->yuv422, composite
-        MC_TRACTOR_SIG(0x15241) // cfg4: composite, ->rgba, affine, ->yuv422, composite
-    default:
-        if (only_bl)
-            k_tractor<true, 0><<<grd, blk, 0, ctx->stream>>>(K);
-        else
-            k_tractor<false, 0><<<grd, blk, 0, ctx->stream>>>(K);
+    const int mode = only_bl ? 1 : (only_nn && has_affine) ? 0 : 2;
+    if (force_generic || d->n_ops == 0)
+        sig = 0;
+#define MC_TRACTOR_SIG(M, S) \
+    case S: \
+        k_tractor<M, S><<<grd, blk, 0, ctx->stream>>>(K); \
+        break;
+    if (mode == 1) {
+        switch (sig) {
+            MC_TRACTOR_SIG(1, 0x1)     // composite
+            MC_TRACTOR_SIG(1, 0x11)    // composite x2
+            MC_TRACTOR_SIG(1, 0x111)   // composite x3
+            MC_TRACTOR_SIG(1, 0x1111)  // composite x4
+            MC_TRACTOR_SIG(1, 0x3)     // luma wipe
+            MC_TRACTOR_SIG(1, 0x13)    // luma wipe, composite (a wipe between two clips under an overlay)
+            MC_TRACTOR_SIG(1, 0x31)    // composite, luma wipe
+            MC_TRACTOR_SIG(1, 0x24)    // ->rgba, affine (rgba consumer: cfg3)
+            MC_TRACTOR_SIG(1, 0x524)   // ->rgba, affine, ->yuv422
+            MC_TRACTOR_SIG(1, 0x5241)  // composite, ->rgba, affine, ->yuv422
+            MC_TRACTOR_SIG(1, 0x1524)  // ->rgba, affine, ->yuv422, composite
+            MC_TRACTOR_SIG(1, 0x15241) // cfg4: composite, ->rgba, affine, ->yuv422, composite
+        default:
+            k_tractor<1, 0><<<grd, blk, 0, ctx->stream>>>(K);
+        }
+    } else if (mode == 0) { // nearest-neighbour sampling (consumer.rescale=nearest: previews)
+        switch (sig) {
+            MC_TRACTOR_SIG(0, 0x24)
+            MC_TRACTOR_SIG(0, 0x524)
+            MC_TRACTOR_SIG(0, 0x15241)
+        default:
+            k_tractor<0, 0><<<grd, blk, 0, ctx->stream>>>(K);
+        }
+    } else {
+        k_tractor<2, 0><<<grd, blk, 0, ctx->stream>>>(K);
     }
 #undef MC_TRACTOR_SIG
     return mc_after_launch(ctx, "k_tractor");

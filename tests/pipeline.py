@@ -24,8 +24,13 @@ def colour_b_rgba(w, h, rgba):
     return out
 
 
-def inputs(position, W, H):
+def inputs(position, W, H, interp="bilinear"):
     f = workloads.cfg4_frame(position, W, H)
+    if interp != "bilinear":  # the same frame with another sampler (consumer.rescale=nearest / bicubic)
+        cfg = workloads.CFG4
+        (k0, r0), (k1, r1) = cfg["affine_k0"], cfg["affine_k1"]
+        r = workloads.lerp_rect(k0, r0, k1, r1, position)
+        f["affine"] = workloads.affine_params(W, H, [r[0] * W, r[1] * H, r[2] * W, r[3] * H, r[4]], position, cfg["rotate_x"], W, H, interp)
     (g1, b1w, b1h), (g2, b2w, b2h) = f["comp1"], f["comp2"]
     return dict(f=f, a=oracle.noise(W, H, position), b1=flip_yuv422(oracle.noise(b1w, b1h, position), b1w, b1h),
                 bc=colour_b_rgba(W, H, workloads.CFG4["colour"]), b3=oracle.noise(b2w, b2h, position))

@@ -25,6 +25,18 @@ def test_cfg4_fused_unfused_oracle(ctx, W, H, frame):
     assert np.array_equal(fus["alpha"], exp["alpha"])
 
 
+@pytest.mark.parametrize("interp", ["nearest", "bicubic"])
+def test_cfg4_other_samplers_fused_unfused_oracle(ctx, interp):
+    """consumer.rescale=nearest takes k_tractor's nearest-only instantiation (transposed pass), bicubic the run-time one."""
+    inp = pipeline.inputs(41, 1920, 1080, interp)
+    exp = pipeline.oracle_chain(inp)
+    unf = pipeline.gpu_unfused(ctx, inp)
+    fus = pipeline.gpu_fused(ctx, inp)
+    assert np.array_equal(fus["out"], unf["out"]) and np.array_equal(fus["alpha"], unf["alpha"])
+    diff = np.abs(fus["out"].astype(int) - exp["out"].astype(int))
+    assert diff.max() <= 2 and (diff > 0).mean() < 1e-4, (int(diff.max()), float((diff > 0).mean()))
+
+
 def test_cfg4_uhd_properties(ctx):
     """Full-size (3840x2160) checks that need no CPU pass over the frame: idempotent inputs,
     untouched regions stay equal to the bottom track, fused == unfused."""
