@@ -237,6 +237,16 @@ CLOSE = [
     # f3: plus/filter_affine.c instantiates the "affine" transition by name over a colour background
     ("wrapper_affine_filter", "rgba", [30], "bilinear",
      A + ["-attach", "affine", "transition.rect=10%/10%:60%x60%:80%", "transition.fix_rotate_x=15", "background=colour:0x20406080"]),
+    # one B track read by two transitions: the composite's deferred op still holds the yuv422 handle when the affine
+    # asks the same frame for rgba (a shared handle is never rewritten: the frame gets a converted copy)
+    ("shared_b_track", "yuv422", [20], "bilinear",
+     A + ["-track", "colour:0x3060c0a0", "out=249", "-transition", "composite", "a_track=0", "b_track=1",
+          "geometry=5%/5%:40%x40%:80%", "-transition", "affine", "a_track=0", "b_track=1", "rect=40%/40%:50%x50%:90%",
+          "fix_rotate_x=10"]),
+    ("shared_b_track_noise", "yuv422", [20], "bilinear",
+     A + AFFINE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=5%/5%:40%x40%:80%", "-transition",
+                     "affine", "a_track=0", "b_track=1", "rect=40%/40%:50%x50%:90%", "fix_rotate_x=10", "-transition",
+                     "composite", "a_track=0", "b_track=1", "geometry=60%/5%:30%x30%:60%"]),
     ("cfg4_1080p", "yuv422", [0, 37], "bilinear",
      A + NOISE_B + ["-transition", "composite", "a_track=0", "b_track=1", "geometry=5%/5%:40%x40%:80%", "-track",
                     "colour:0x3060c0a0", "out=599", "-transition", "affine", "a_track=0", "b_track=2",
