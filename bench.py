@@ -315,6 +315,43 @@ class Timed:
         ms = lib.mltcuda_event_elapsed_ms(self.ev0, self.ev1)
         return ms, sum(w.launches() for w in workers) - l0
 
+    def capture(self, fn):
+        """Record one step (all its launches on all worker contexts) into a CUDA graph: the other workers fork
+        from workers[0]'s capturing stream through an event and join back before the capture ends."""
+        from mlt_b200 import abi
+        lib, workers = self.lib, self.workers
+        for w in workers:
+            w.sync()
+        fork = lib.mltcuda_event_create()
+        joins = [lib.mltcuda_event_create() for _ in workers[1:]]
+        abi.check(lib.mltcuda_graph_begin(workers[0].h), "graph_begin")
+        lib.mltcuda_event_record(workers[0].h, fork)
+        for w in workers[1:]:
+            abi.check(lib.mltcuda_ctx_wait_event(w.h, fork), "wait_event")
+        fn()
+        for w, j in zip(workers[1:], joins):
+            lib.mltcuda_event_record(w.h, j)
+            abi.check(lib.mltcuda_ctx_wait_event(workers[0].h, j), "wait_event")
+        g = lib.mltcuda_graph_end(workers[0].h)
+        if not g:
+            raise abi.MltCudaError("graph capture: " + lib.mltcuda_last_error().decode())
+        return g
+
+    def run_graph(self, g, steps, dist):
+        """`steps` replays of a captured step, timed with events on workers[0]'s stream."""
+        from mlt_b200 import abi
+        lib, w0 = self.lib, self.workers[0]
+        abi.check(lib.mltcuda_graph_launch(w0.h, g), "graph_launch")  # first replay uploads the graph
+        w0.sync()
+        dist.barrier()
+        lib.mltcuda_event_record(w0.h, self.ev0)
+        for _ in range(steps):
+            abi.check(lib.mltcuda_graph_launch(w0.h, g), "graph_launch")
+        lib.mltcuda_event_record(w0.h, self.ev1)
+        w0.sync()
+        dist.barrier()
+        return lib.mltcuda_event_elapsed_ms(self.ev0, self.ev1), int(lib.mltcuda_graph_kernel_nodes(g)) * steps
+
 
 def cfg4_setup(lib, ctx, first, F, w, h):
     """Resident tracks + op lists for F consecutive timeline frames of cfg4 at w x h."""
@@ -376,7 +413,7 @@ def cfg4_steps(lib, S, workers, repeat):
     return full, fused_only
 
 
-def extra_1080p(lib, ctx, workers, dist, steps):
+def extra_1080p(lib, ctx, workers, dist, steps, graph=True):
     """Device legs of the other BASELINE.json configurations at 1080p (producers inside the timed region)."""
     from mlt_b200 import abi, workloads
     w, h, F, rep = 1920, 1080, 64, 4
@@ -399,7 +436,10 @@ def extra_1080p(lib, ctx, workers, dist, steps):
                     produce(i, c)
                     per_frame(i, c)
         step()
-        ms, _ = timed.run(step, steps, dist)
+        if graph:
+            ms, _ = timed.run_graph(timed.capture(step), steps, dist)
+        else:
+            ms, _ = timed.run(step, steps, dist)
         out[name] = round(dist.world * F * rep * steps / (dist.reduce(ms, "MAX") / 1e3), 1)
 
     # cfg1: composite, full frame, 50 % (SSE2 case 1)
@@ -439,7 +479,10 @@ def extra_1080p(lib, ctx, workers, dist, steps):
     S = cfg4_setup(lib, ctx, 0, F, w, h)
     full, _ = cfg4_steps(lib, S, workers, rep)
     full()
-    ms, _ = timed.run(full, steps, dist)
+    if graph:
+        ms, _ = timed.run_graph(timed.capture(full), steps, dist)
+    else:
+        ms, _ = timed.run(full, steps, dist)
     out["cfg4_4track_1080p"] = round(dist.world * F * rep * steps / (dist.reduce(ms, "MAX") / 1e3), 1)
     return out
 
@@ -464,14 +507,25 @@ def run_ours(args, dist):
     timed = Timed(lib, workers)
 
     # ---- device leg: producers + fused pass --------------------------------------------------------
+    # A step (512 frames x 5 launches) is recorded once into a CUDA graph and replayed: at 5-8 us of host time per
+    # launch the python loop, not the GPU, would set the pace (and eight ranks would compete for the host cores).
+    # --no-graph times the plain launch loop instead.
     for _ in range(max(1, args.warmup // 2)):
         full()
     clocks = ClockSampler(dev)
-    clocks.start()
-    ms, launches = timed.run(full, args.steps, dist)
-    # ---- the fused kernel alone (roofline) -----------------------------------------------------------
-    fused_only()
-    ms_k, launches_k = timed.run(fused_only, args.steps, dist)
+    if args.no_graph:
+        clocks.start()
+        ms, launches = timed.run(full, args.steps, dist)
+        fused_only()
+        ms_k, launches_k = timed.run(fused_only, args.steps, dist)
+    else:
+        g_full, g_fused = timed.capture(full), timed.capture(fused_only)
+        for _ in range(max(1, args.warmup // 2)):
+            timed.run_graph(g_full, 1, dist)
+        clocks.start()
+        ms, launches = timed.run_graph(g_full, args.steps, dist)
+        # ---- the fused kernel alone (roofline) -------------------------------------------------------
+        ms_k, launches_k = timed.run_graph(g_fused, args.steps, dist)
     clk = clocks.stop()
     ms_max = dist.reduce(ms, "MAX")
     total_launches = int(dist.reduce(launches, "SUM"))
@@ -516,7 +570,7 @@ def run_ours(args, dist):
         roofline["issue_bound"] = {"warp_instr_per_launch": winstr, "min_us_per_launch": round(min_us, 2),
                                    "frac": round(min_us / (avg_launch_s * 1e6), 4),
                                    "hbm_frac_at_full_issue": round(alg_per_launch / (min_us * 1e-6) / 1e9 / peak, 4)}
-    extra = extra_1080p(lib, ctx, workers, dist, max(2, min(5, args.steps))) if not args.no_extra else None
+    extra = extra_1080p(lib, ctx, workers, dist, max(2, min(5, args.steps)), not args.no_graph) if not args.no_extra else None
 
     # ---- end to end through the C-ABI: host (pinned) tracks in, composited frame out ------------------
     e2e_abi = None
@@ -578,6 +632,7 @@ def run_ours(args, dist):
                 "arm": {"timed_region": "per frame 3 k_noise (tracks 0, 1, 3) + k_mirror_flip (track 1) + 1 k_tractor = the melt graph's "
                                         "device work; colour track resident (constant)",
                         "launches_per_frame": round(total_launches / (dist.world * FRAMES_PER_STEP * args.steps), 3),
+                        "submission": "plain launch loop" if args.no_graph else "one CUDA graph per step (512 frames), replayed",
                         "worker_streams": len(workers), "parallelism": f"frame-sharded x{dist.world}, no collective"},
                 "e2e": e2e, "gpu_launches": total_launches, "roofline": roofline, "clocks": clk}
         if e2e_resident:
@@ -669,6 +724,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the 1080p cfg1..cfg4 device legs")
     ap.add_argument("--no-e2e-abi", action="store_true", help="skip the C-ABI-only end-to-end leg")
+    ap.add_argument("--no-graph", action="store_true", help="device legs: a python launch loop instead of CUDA-graph replays")
     ap.add_argument("--no-melt", action="store_true", help="skip the melt + module legs (profiler runs: the device legs only)")
     ap.add_argument("--streams", type=int, default=2, help="worker contexts (streams) per GPU on the device leg, 1..8")
     ap.add_argument("--melt-threads", type=int, default=0, help="real_time=-T of the melt + module leg (0 = auto)")

@@ -92,6 +92,19 @@ int mltcuda_upload_staged(mltcuda_ctx *ctx, void *dst_dev, const void *src_host,
 int mltcuda_copy(mltcuda_ctx *ctx, void *dst_dev, const void *src_dev, size_t bytes);
 int mltcuda_memset(mltcuda_ctx *ctx, void *dst_dev, int value, size_t bytes);
 
+/* CUDA graphs.  Everything submitted to `ctx` between _begin and _end -- and to any other context that joins through
+ * mltcuda_ctx_wait_event on an event recorded in between, and is joined back the same way before _end -- is
+ * recorded instead of executed; mltcuda_graph_launch replays the whole sequence with one call (a launch-bound
+ * per-frame loop no longer depends on the host's launch rate).  Buffers and parameters are baked in: a graph
+ * replays exactly the frames it recorded.  No allocation, synchronisation or first-use initialisation may happen
+ * inside the capture (run the sequence once before recording it). */
+typedef struct mltcuda_graph mltcuda_graph;
+int mltcuda_graph_begin(mltcuda_ctx *ctx);
+mltcuda_graph *mltcuda_graph_end(mltcuda_ctx *ctx); /* NULL on error */
+int mltcuda_graph_launch(mltcuda_ctx *ctx, mltcuda_graph *g);
+uint64_t mltcuda_graph_kernel_nodes(const mltcuda_graph *g);
+void mltcuda_graph_destroy(mltcuda_graph *g);
+
 /* Is every byte of a device plane 0xff?  -- is_opaque() of src/modules/core/transition_luma.c:34-41 as a
  * stream-ordered query: _query enqueues the reduction and the copy of its verdict to pinned host
  * memory; after the next mltcuda_ctx_sync / event wait behind it, _result returns 1 (all 0xff) or 0.

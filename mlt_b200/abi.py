@@ -101,6 +101,11 @@ SIGNATURES = {
     "mltcuda_download": (C.c_int, [vp, vp, vp, sz]),
     "mltcuda_copy": (C.c_int, [vp, vp, vp, sz]),
     "mltcuda_memset": (C.c_int, [vp, vp, C.c_int, sz]),
+    "mltcuda_graph_begin": (C.c_int, [vp]),
+    "mltcuda_graph_end": (vp, [vp]),
+    "mltcuda_graph_launch": (C.c_int, [vp, vp]),
+    "mltcuda_graph_kernel_nodes": (C.c_uint64, [vp]),
+    "mltcuda_graph_destroy": (None, [vp]),
     "mltcuda_plane_opaque_query": (C.c_int, [vp, vp, sz]),
     "mltcuda_plane_opaque_result": (C.c_int, [vp]),
     "mltcuda_event_create": (vp, []),

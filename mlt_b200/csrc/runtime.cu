@@ -340,6 +340,79 @@ int mltcuda_plane_opaque_result(const mltcuda_ctx *ctx)
     return ctx && ctx->opaque_host ? *ctx->opaque_host == 0 : 0;
 }
 
+// ---- CUDA graphs: a launch-bound sequence (hundreds of per-frame launches on one or several contexts) recorded
+// once and replayed with one call, so the host's launch rate is out of the picture.
+struct mltcuda_graph
+{
+    cudaGraph_t graph;
+    cudaGraphExec_t exec;
+    size_t kernel_nodes;
+};
+
+int mltcuda_graph_begin(mltcuda_ctx *ctx)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_CHECK(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+    return 0;
+}
+
+mltcuda_graph *mltcuda_graph_end(mltcuda_ctx *ctx)
+{
+    if (mc_use(ctx))
+        return nullptr;
+    mltcuda_graph *g = new mltcuda_graph();
+    g->graph = nullptr, g->exec = nullptr, g->kernel_nodes = 0;
+    cudaError_t e = cudaStreamEndCapture(ctx->stream, &g->graph);
+    if (e == cudaSuccess)
+        e = cudaGraphInstantiate(&g->exec, g->graph, 0);
+    if (e != cudaSuccess) {
+        mltcuda_set_error("graph capture / instantiate -> %s", cudaGetErrorString(e));
+        cudaGetLastError();
+        if (g->graph)
+            cudaGraphDestroy(g->graph);
+        delete g;
+        return nullptr;
+    }
+    size_t n = 0;
+    if (cudaGraphGetNodes(g->graph, nullptr, &n) == cudaSuccess && n) {
+        std::vector<cudaGraphNode_t> nodes(n);
+        cudaGraphGetNodes(g->graph, nodes.data(), &n);
+        for (size_t i = 0; i < n; i++) {
+            cudaGraphNodeType t;
+            if (cudaGraphNodeGetType(nodes[i], &t) == cudaSuccess && t == cudaGraphNodeTypeKernel)
+                g->kernel_nodes++;
+        }
+    }
+    return g;
+}
+
+int mltcuda_graph_launch(mltcuda_ctx *ctx, mltcuda_graph *g)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!g || !g->exec, "null graph");
+    MC_CHECK(cudaGraphLaunch(g->exec, ctx->stream));
+    ctx->launches += g->kernel_nodes;
+    return 0;
+}
+
+uint64_t mltcuda_graph_kernel_nodes(const mltcuda_graph *g)
+{
+    return g ? g->kernel_nodes : 0;
+}
+
+void mltcuda_graph_destroy(mltcuda_graph *g)
+{
+    if (!g)
+        return;
+    if (g->exec)
+        cudaGraphExecDestroy(g->exec);
+    if (g->graph)
+        cudaGraphDestroy(g->graph);
+    delete g;
+}
+
 mltcuda_event *mltcuda_event_create(void)
 {
     mltcuda_event *ev = new mltcuda_event();

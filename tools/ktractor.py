@@ -32,6 +32,7 @@ if __name__ == "__main__":
     ap.add_argument("--h", type=int, default=2160)
     ap.add_argument("--distinct", type=int, default=32)
     ap.add_argument("--repeat", type=int, default=8)
+    ap.add_argument("--graph", action="store_true", help="replay the step from a CUDA graph instead of launching from python")
     ap.add_argument("--interp", default="bilinear", help="affine sampler: nearest | bilinear | bicubic (non-bilinear = the ONLY_BL=false instantiation)")
     a = ap.parse_args()
     lib = abi.load()
@@ -43,7 +44,10 @@ if __name__ == "__main__":
     full, fused_only = bench.cfg4_steps(lib, S, workers, a.repeat)
     timed = bench.Timed(lib, workers)
     fused_only()
-    ms, launches = timed.run(fused_only, a.steps, NoDist())
+    if a.graph:
+        ms, launches = timed.run_graph(timed.capture(fused_only), a.steps, NoDist())
+    else:
+        ms, launches = timed.run(fused_only, a.steps, NoDist())
     cov = [bench.covered_pixels(f["affine"], a.w, a.h) for f in S["frames"]]
     alg = float(np.mean([a.w * a.h * 5 + S["b1b"] + S["b3b"] + 4 * c for c in cov]))
     us = ms * 1e3 / launches
