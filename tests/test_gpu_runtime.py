@@ -76,3 +76,38 @@ def test_plane_opaque_query(ctx, nbytes):
         abi.check(lib.mltcuda_plane_opaque_query(ctx.h, d2.ptr, nbytes))
         ctx.sync()
         assert lib.mltcuda_plane_opaque_result(ctx.h) == 0, pos
+
+
+def test_graph_capture_replays_launches_on_two_contexts():
+    """mltcuda_graph_*: a sequence recorded on one context, with a second context forked in and joined back through
+    events, replays with one call and produces what the plain launches produce."""
+    lib = abi.load()
+    a, b = Context(0), Context(0)
+    try:
+        w, h = 256, 64
+        d1, d2, ref1, ref2 = a.alloc(w * h * 2), b.alloc(w * h * 2), a.alloc(w * h * 2), a.alloc(w * h * 2)
+        abi.check(lib.mltcuda_noise(a.h, ref1.ptr, w, h, 7, 1, 0))  # also warms the generator's tables
+        abi.check(lib.mltcuda_noise(a.h, ref2.ptr, w, h, 8, 1, 0))
+        abi.check(lib.mltcuda_noise(b.h, d2.ptr, w, h, 1, 1, 0))
+        a.sync(), b.sync()
+        fork, join = lib.mltcuda_event_create(), lib.mltcuda_event_create()
+        abi.check(lib.mltcuda_graph_begin(a.h))
+        lib.mltcuda_event_record(a.h, fork)
+        abi.check(lib.mltcuda_ctx_wait_event(b.h, fork))
+        abi.check(lib.mltcuda_noise(a.h, d1.ptr, w, h, 7, 1, 0))
+        abi.check(lib.mltcuda_noise(b.h, d2.ptr, w, h, 8, 1, 0))
+        lib.mltcuda_event_record(b.h, join)
+        abi.check(lib.mltcuda_ctx_wait_event(a.h, join))
+        g = lib.mltcuda_graph_end(a.h)
+        assert g, lib.mltcuda_last_error()
+        assert lib.mltcuda_graph_kernel_nodes(g) == 2
+        n0 = a.launches()
+        abi.check(lib.mltcuda_memset(a.h, d1.ptr, 0, w * h * 2))
+        abi.check(lib.mltcuda_graph_launch(a.h, g))
+        a.sync()
+        assert a.launches() == n0 + 2
+        assert np.array_equal(a.get(d1, (w * h * 2,)), a.get(ref1, (w * h * 2,)))
+        assert np.array_equal(a.get(d2, (w * h * 2,)), a.get(ref2, (w * h * 2,)))
+        lib.mltcuda_graph_destroy(g)
+    finally:
+        a.close(), b.close()
