@@ -529,6 +529,12 @@ def run_ours(args, dist):
         fused_only()
         ms_k, launches_k = timed.run(fused_only, args.steps, dist)
     clk = clocks.stop()
+    # every rank samples its own GPU: the slowest rank sets `value`, so its clocks and throttle reasons are the ones to show
+    bits = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+    if dist.world > 1:
+        clk["sm_mhz_min_over_ranks"] = int(dist.reduce(clk.get("sm_mhz") or 0, "MIN"))
+        clk["reasons"] = [n for n in bits if dist.reduce(1.0 if n in clk.get("reasons", []) else 0.0, "MAX") > 0]
+        clk["ms_per_step_fastest_rank"] = round(dist.reduce(ms, "MIN") / args.steps, 4)
     ms_max = dist.reduce(ms, "MAX")
     total_launches = int(dist.reduce(launches, "SUM"))
     value = dist.world * FRAMES_PER_STEP * args.steps / (ms_max / 1e3)
