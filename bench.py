@@ -208,6 +208,9 @@ class ClockSampler:
         self.sm, self.reason_bits, self.max_mhz = [], 0, None
 
     def start(self):
+        if os.environ.get("MLTBENCH_NO_CLOCKS"):  # diagnostic: no NVML polling during the timed region
+            self.proc = None
+            return
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -353,13 +356,14 @@ class Timed:
         return lib.mltcuda_event_elapsed_ms(self.ev0, self.ev1), int(lib.mltcuda_graph_kernel_nodes(g)) * steps
 
 
-def cfg4_setup(lib, ctx, first, F, w, h):
+def cfg4_setup(lib, ctx, positions, w, h):
     """Resident tracks + op lists for F consecutive timeline frames of cfg4 at w x h."""
     from mlt_b200 import abi, workloads
-    frames = [workloads.cfg4_frame(first + i, w, h) for i in range(F)]
+    F = len(positions)
+    frames = [workloads.cfg4_frame(p, w, h) for p in positions]
     (g1, b1w, b1h), (g2, b2w, b2h) = frames[0]["comp1"], frames[0]["comp2"]
     fb, b1b, b3b = w * h * 2, b1w * b1h * 2, b2w * b2h * 2
-    S = dict(frames=frames, fb=fb, b1b=b1b, b3b=b3b, b1=(b1w, b1h), b3=(b2w, b2h), first=first, F=F, w=w, h=h)
+    S = dict(frames=frames, fb=fb, b1b=b1b, b3b=b3b, b1=(b1w, b1h), b3=(b2w, b2h), pos=list(positions), F=F, w=w, h=h)
     S["d_in"], S["d_b1"], S["d_b3"] = ctx.alloc(F * fb), ctx.alloc(F * b1b), ctx.alloc(F * b3b)
     S["d_b1raw"] = ctx.alloc(F * b1b)  # track 1 before its mirror:flip
     S["d_bc"], d_bcy, d_bca = ctx.alloc(w * h * 4), ctx.alloc(fb), ctx.alloc(w * h)
@@ -377,17 +381,17 @@ def cfg4_setup(lib, ctx, first, F, w, h):
 def cfg4_steps(lib, S, workers, repeat):
     """(full step: producers + fused pass per frame, fused pass alone) as closures."""
     from mlt_b200 import abi
-    F, w, h, fb, b1b, b3b, first = S["F"], S["w"], S["h"], S["fb"], S["b1b"], S["b3b"], S["first"]
+    F, w, h, fb, b1b, b3b, pos = S["F"], S["w"], S["h"], S["fb"], S["b1b"], S["b3b"], S["pos"]
     (b1w, b1h), (b3w, b3h) = S["b1"], S["b3"]
     nw = len(workers)
 
     def produce(i, c):
         # the graph's producers and its track-1 filter: noise at the frame's position on tracks 0, 1 and 3
         # (producer_noise.c), mirror:flip on track 1 (filter_mirror.c) -- all on the device, as the module runs them
-        rc = lib.mltcuda_noise(c.h, S["d_in"].at(i * fb), w, h, first + i, 1, 0)
-        rc |= lib.mltcuda_noise(c.h, S["d_b1raw"].at(i * b1b), b1w, b1h, first + i, 1, 0)
+        rc = lib.mltcuda_noise(c.h, S["d_in"].at(i * fb), w, h, pos[i], 1, 0)
+        rc |= lib.mltcuda_noise(c.h, S["d_b1raw"].at(i * b1b), b1w, b1h, pos[i], 1, 0)
         rc |= lib.mltcuda_mirror_flip(c.h, S["d_b1"].at(i * b1b), None, S["d_b1raw"].at(i * b1b), None, b1w, b1h)
-        rc |= lib.mltcuda_noise(c.h, S["d_b3"].at(i * b3b), b3w, b3h, first + i, 1, 0)
+        rc |= lib.mltcuda_noise(c.h, S["d_b3"].at(i * b3b), b3w, b3h, pos[i], 1, 0)
         if rc:
             abi.check(rc, "producers")
 
@@ -476,7 +480,7 @@ def extra_1080p(lib, ctx, workers, dist, steps, graph=True):
             abi.check(rc, "cfg3")
     leg("cfg3_affine_rgba_1080p", cfg3)
     # cfg4 at 1080p
-    S = cfg4_setup(lib, ctx, 0, F, w, h)
+    S = cfg4_setup(lib, ctx, list(range(F)), w, h)
     full, _ = cfg4_steps(lib, S, workers, rep)
     full()
     if graph:
@@ -500,8 +504,9 @@ def run_ours(args, dist):
     workers = [Context(dev) for _ in range(max(1, min(8, args.streams)))]
     ctx = workers[0]
     F = DISTINCT
-    first = workloads.shard_frames(dist.rank, dist.world, F)[0]  # each rank renders its own slice of the timeline
-    S = cfg4_setup(lib, ctx, first, F, W, H)
+    # each rank renders its own frames of the timeline, dealt round-robin so that every rank has the same cost profile
+    positions = workloads.interleaved_frames(dist.rank, dist.world, F)
+    S = cfg4_setup(lib, ctx, positions, W, H)
     fb, b1b, b3b, frames = S["fb"], S["b1b"], S["b3b"], S["frames"]
     full, fused_only = cfg4_steps(lib, S, workers, REPEAT)
     timed = Timed(lib, workers)
@@ -641,7 +646,7 @@ def run_ours(args, dist):
                                         "device work; colour track resident (constant)",
                         "launches_per_frame": round(total_launches / (dist.world * FRAMES_PER_STEP * args.steps), 3),
                         "submission": "plain launch loop" if args.no_graph else "one CUDA graph per step (512 frames), replayed",
-                        "worker_streams": len(workers), "parallelism": f"frame-sharded x{dist.world}, no collective"},
+                        "worker_streams": len(workers), "parallelism": f"frame-sharded x{dist.world} (timeline frames dealt round-robin, stride {max(8, dist.world)}), no collective"},
                 "e2e": e2e, "gpu_launches": total_launches, "roofline": roofline, "clocks": clk}
         if e2e_resident:
             line["e2e_resident"] = e2e_resident

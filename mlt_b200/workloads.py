@@ -188,3 +188,13 @@ def cfg3_frame(position, W=1920, H=1080, cfg=CFG3):
     r = lerp_rect(k0, r0, k1, r1, position)
     rect_px = [r[0] * W, r[1] * H, r[2] * W, r[3] * H, r[4]]
     return affine_params(W, H, rect_px, position, cfg["rotate_x"], W, H, "bilinear")
+
+
+def interleaved_frames(rank, world, frames_per_rank, window_ranks=8):
+    """Frame-parallel sharding with EQUAL work per GPU: the cost of a cfg4 frame drifts along the timeline (the
+    keyframed affine rectangle grows), so contiguous blocks would give later ranks heavier frames and a max-over-ranks
+    timing would read that as a scaling loss.  The benchmark therefore always works on the same window of
+    frames_per_rank x max(world, window_ranks) timeline frames, dealt round-robin: rank r renders frames
+    r, r + S, r + 2S, ... with S = max(world, window_ranks) -- every rank (and the 1-GPU run) sees the same cost profile."""
+    stride = max(world, window_ranks)
+    return [i * stride + rank for i in range(frames_per_rank)]

@@ -36,7 +36,7 @@ def _worker(rank, world, port, F, W, H, q):
     from mlt_b200 import workloads
     d = bench.Dist()  # the class bench.py uses: gloo barrier + reductions
     assert (d.rank, d.world) == (rank, world)
-    frames = workloads.shard_frames(d.rank, d.world, F)
+    frames = workloads.interleaved_frames(d.rank, d.world, F)  # what bench.py deals to each rank
     mine = [(f, _digest(f, W, H)) for f in frames]
     d.barrier()
     ms_max = d.reduce(10.0 + rank, "MAX")   # timing: max over ranks
@@ -61,11 +61,14 @@ def test_two_gloo_ranks_shard_frames_like_bench():
         p.join(timeout=60)
         assert p.exitcode == 0
     sys.path.insert(0, os.path.join(ROOT, "tests"))
-    expected = {f: _digest(f, W, H) for f in range(world * F)}
+    from mlt_b200 import workloads
+    want = sorted(f for r in range(world) for f in workloads.interleaved_frames(r, world, F))
+    assert len(set(want)) == world * F  # disjoint
+    expected = {f: _digest(f, W, H) for f in want}
     for rank, ms_max, total, gathered in results:
         assert ms_max == 11.0 and total == world * F
         got = dict(x for part in gathered for x in part)
-        assert sorted(got) == list(range(world * F))  # disjoint and complete
+        assert sorted(got) == want  # disjoint and complete
         assert got == expected
 
 
@@ -77,3 +80,16 @@ def test_shard_frames_partitions_every_step():
             for r in range(world):
                 seen += workloads.shard_frames(r, world, 32, step)
             assert seen == list(range(step * world * 32, (step + 1) * world * 32))
+
+
+def test_interleaved_frames_give_every_rank_the_same_window():
+    """bench.py's dealing: disjoint across ranks, and every rank (at any world size up to 8) walks the same
+    32 x 8-frame window of the timeline with stride 8, so per-GPU work does not depend on the rank or on N."""
+    from mlt_b200 import workloads
+    for world in (1, 2, 4, 8, 16):
+        stride = max(world, 8)
+        allf = [workloads.interleaved_frames(r, world, 32) for r in range(world)]
+        flat = [f for fr in allf for f in fr]
+        assert len(set(flat)) == len(flat)
+        for r, fr in enumerate(allf):
+            assert fr == [i * stride + r for i in range(32)]

@@ -40,7 +40,7 @@ if __name__ == "__main__":
     if a.interp != "bilinear":
         _ap = workloads.affine_params
         workloads.affine_params = lambda *x, **k: _ap(*x[:7], a.interp)
-    S = bench.cfg4_setup(lib, workers[0], 0, a.distinct, a.w, a.h)
+    S = bench.cfg4_setup(lib, workers[0], workloads.interleaved_frames(0, 1, a.distinct), a.w, a.h)
     full, fused_only = bench.cfg4_steps(lib, S, workers, a.repeat)
     timed = bench.Timed(lib, workers)
     fused_only()
