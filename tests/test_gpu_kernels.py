@@ -430,3 +430,48 @@ def test_mirror_flip(ctx, w, h, alpha):
     if alpha:
         assert np.array_equal(ctx.get(d_alo, (w * h,)), np.ascontiguousarray(al.reshape(h, w)[:, ::-1]).reshape(-1))
     assert ctx.lib.mltcuda_mirror_flip(ctx.h, d_dst.ptr, None, d_src.ptr, None, 7, 4) == abi.E_UNSUPPORTED
+
+
+def _ref_resize_pad(src, iw, ih, ow, oh, bpp, fill_px, yuv):
+    """resize_image (filter_resize.c:65-137): fill, then the input rows copied at the centred offset."""
+    out = np.tile(np.array(fill_px, np.uint8), ow * oh).reshape(oh, ow * bpp)
+    off_x = (ow - iw) // 2 * bpp
+    if yuv:
+        off_x -= off_x % 4
+    off_y = (oh - ih) // 2
+    out[off_y:off_y + ih, off_x:off_x + iw * bpp] = src.reshape(ih, iw * bpp)
+    return out.reshape(-1)
+
+
+@pytest.mark.parametrize("fmt,bpp,iw,ih,ow,oh,alpha", [(3, 2, 1440, 1080, 1920, 1080, 0), (3, 2, 630, 355, 632, 355, 7),
+                                                      (2, 4, 100, 50, 128, 72, 200), (10, 8, 64, 40, 96, 54, 255),
+                                                      (1, 3, 33, 20, 40, 30, 0), (0, 1, 101, 37, 128, 41, 99)])
+def test_resize_pad(ctx, fmt, bpp, iw, ih, ow, oh, alpha):
+    rng = np.random.default_rng(iw * 7 + ow)
+    src = rng.integers(0, 256, iw * ih * bpp).astype(np.uint8)
+    fill = {3: [16, 128], 2: [0, 0, 0, alpha], 10: [0, 0, 0, 0, 0, 0, 0, alpha], 1: [0, 0, 0], 0: [alpha]}[fmt]
+    if fmt == 0:  # resize_alpha (:30-63): offset_x rounded down to even
+        exp = np.full((oh, ow), alpha, np.uint8)
+        ox, oy = (ow - iw) // 2, (oh - ih) // 2
+        ox -= ox % 2
+        exp[oy:oy + ih, ox:ox + iw] = src.reshape(ih, iw)
+        exp = exp.reshape(-1)
+    else:
+        exp = _ref_resize_pad(src, iw, ih, ow, oh, bpp, fill, fmt == 3)
+    d_src, d_dst = ctx.put(src), ctx.alloc(ow * oh * bpp)
+    abi.check(ctx.lib.mltcuda_resize_pad(ctx.h, d_dst.ptr, ow, oh, d_src.ptr, iw, ih, fmt, alpha))
+    assert np.array_equal(ctx.get(d_dst, (ow * oh * bpp,)), exp)
+
+
+@pytest.mark.parametrize("iw,ih,ow,oh", [(1920, 1080, 576, 324), (720, 576, 1920, 1080), (101, 57, 64, 33)])
+def test_rescale_alpha(ctx, iw, ih, ow, oh):
+    """scale_alpha (filter_rescale.c:122-147): nearest neighbour in 16.16 fixed point, sampled at pixel centres."""
+    rng = np.random.default_rng(iw + oh)
+    src = rng.integers(0, 256, iw * ih).astype(np.uint8)
+    ox, oy = (iw << 16) // ow, (ih << 16) // oh
+    ys = ((oy >> 1) + np.arange(oh) * oy) >> 16
+    xs = ((ox >> 1) + np.arange(ow) * ox) >> 16
+    exp = src.reshape(ih, iw)[ys][:, xs].reshape(-1)
+    d_src, d_dst = ctx.put(src), ctx.alloc(ow * oh)
+    abi.check(ctx.lib.mltcuda_rescale_alpha(ctx.h, d_dst.ptr, ow, oh, d_src.ptr, iw, ih))
+    assert np.array_equal(ctx.get(d_dst, (ow * oh,)), exp)
