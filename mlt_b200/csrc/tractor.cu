@@ -91,24 +91,27 @@ __host__ __device__ constexpr int sig_first(uint32_t sig, uint32_t code)
 #ifndef K5_MINB
 #define K5_MINB 8
 #endif
+#ifndef K5_ROWS
+#define K5_ROWS 4 // rows (= warps) per CTA
+#endif
 #ifndef K5_GEN_MINB
 #define K5_GEN_MINB 8
 #endif
 // MODE: 1 = every affine op samples bilinearly, 0 = every affine op samples nearest, 2 = anything else (sampler chosen
 // at run time).  Modes 0 and 1 compile exactly one sampler in and take the warp-transposed affine pass.
 template <int MODE, uint32_t SIG>
-__global__ void __launch_bounds__(128, MODE != 2 ? (SIG ? K5_MINB : K5_GEN_MINB) : 2) k_tractor(const __grid_constant__ TractorK K)
+__global__ void __launch_bounds__(32 * K5_ROWS, MODE != 2 ? (SIG ? K5_MINB : K5_GEN_MINB) * 4 / K5_ROWS : 2) k_tractor(const __grid_constant__ TractorK K)
 {
     constexpr bool ONLY_BL = MODE != 2; // "one sampler" (name kept from when bilinear was the only such mode)
     // 2-D CTA: 32 groups (256 px) x 4 rows (128-thread CTAs balance the heavy affine tiles better than 256: +2.8%) -- no div/mod, and the B taps of neighbouring rows share L1
     const int c = blockIdx.x * 32 + threadIdx.x;
-    const int r = blockIdx.y * 4 + threadIdx.y;
+    const int r = blockIdx.y * K5_ROWS + threadIdx.y;
     // blockDim.x == 32: a warp is 32 consecutive groups (256 px) of one row
     const bool valid = c < (K.width >> 3) && r < K.height;
     const bool fullwarp = __ballot_sync(0xffffffffu, valid) == 0xffffffffu;
     if (!valid)
         return;
-    __shared__ uint32_t s_xpose[4][256]; // per-warp staging for the transposed affine pass
+    __shared__ uint32_t s_xpose[K5_ROWS][256]; // per-warp staging for the transposed affine pass
     const int b = blockIdx.z;
     const int col0 = c * 8;
     const size_t pix0 = (size_t) r * K.width + col0;
@@ -450,8 +453,8 @@ extern "C" int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d)
         }
     }
     MC_BADARG(fmt != d->out_format, "out_format does not match the format the op list ends in");
-    MC_BADARG((d->height + 3) / 4 > 65535 || K.batch > 65535, "frame too tall / batch too large for one launch");
-    dim3 blk(32, 4, 1), grd((d->width / 8 + 31) / 32, (d->height + 4 - 1) / 4, K.batch);
+    MC_BADARG((d->height + K5_ROWS - 1) / K5_ROWS > 65535 || K.batch > 65535, "frame too tall / batch too large for one launch");
+    dim3 blk(32, K5_ROWS, 1), grd((d->width / 8 + 31) / 32, (d->height + K5_ROWS - 1) / K5_ROWS, K.batch);
     // op-list signature (see k_tractor): specialised instantiations for the common graph shapes
     uint32_t sig = 0;
     bool has_affine = false;
