@@ -30,7 +30,7 @@ extern "C" {
 #pragma GCC visibility push(default)
 #endif
 
-#define MLTCUDA_ABI_VERSION 1
+#define MLTCUDA_ABI_VERSION 2 /* 2: mltcuda_rescale_yuv422 gained batch + strides; graphs, resize pad, mirror, opacity query, cross-context ordering added */
 
 /* error codes beyond cudaError_t (which are < 1000) */
 #define MLTCUDA_E_BADARG 10001

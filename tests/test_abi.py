@@ -28,7 +28,7 @@ def test_header_symbols_all_exported_and_typed():
 
 def test_abi_version_and_no_device_error():
     lib = abi.load()
-    assert lib.mltcuda_abi_version() == 1
+    assert lib.mltcuda_abi_version() == 2
     if lib.mltcuda_device_count() == 0:
         # the product path fails loudly without a GPU: no CPU fallback
         assert not lib.mltcuda_ctx_create(0)
