@@ -317,6 +317,32 @@ int mltcuda_tractor(mltcuda_ctx *ctx, const mltcuda_tractor_desc *d);
  * src/modules/core/producer_noise.c:37-51,78-126 and producer_colour.c:60-274.               */
 int mltcuda_noise(mltcuda_ctx *ctx, uint8_t *dst_yuv422, int width, int height, int position,
                   int batch, size_t dst_bstride);
+/* mltcuda_noise for callers that must not allocate.  No counterpart in the reference (its producer
+ * has no device memory to manage); same arguments, same bytes out as mltcuda_noise.
+ *
+ * Who needs it: a real_time worker thread in mid-playback, for which the device-wide lock and GPU
+ * drain of a cudaMalloc/cudaFree would stall every other worker's stream; a host application that
+ * has given all device memory to its own pool, or runs inside a fixed MIG/MPS memory budget, where
+ * an allocation may fail at a point that cannot recover.  mltcuda_noise cudaMalloc's its skip-ahead
+ * tables per context; this entry point keeps them in a static __device__ array inside the library
+ * image instead (MLTCUDA_NOISE_STATIC_BYTES on every GPU that loads the library, held until the
+ * process exits) and calls no cudaMalloc, cudaFree or allocating library routine, ever.
+ *
+ * Limits: width*height <= MLTCUDA_NOISE_STATIC_MAX_PIXELS per frame (the reach of the tables'
+ * 32-bit skip-ahead) and batch <= MLTCUDA_NOISE_STATIC_MAX_BATCH; anything larger is refused with
+ * MLTCUDA_E_BADARG and a message, nothing is launched.  At most 64 GPUs per process.
+ *
+ * First call on each GPU: looks up the array's address on that GPU and fills the tables with a
+ * blocking copy on ctx's stream (thread-safe).  Make that call once per GPU at start-up, outside
+ * any stream capture.  Later calls only launch the kernel.
+ *
+ * Sharing: all contexts of a GPU use the one array.  After the first call it is only read, so
+ * calls may overlap on the GPU and nothing needs clearing between them. */
+#define MLTCUDA_NOISE_STATIC_BYTES 67584 /* 2 generators x (4096 + 4096 + 256) x 4 bytes */
+#define MLTCUDA_NOISE_STATIC_MAX_PIXELS 2147483647LL
+#define MLTCUDA_NOISE_STATIC_MAX_BATCH 65535
+int mltcuda_noise_static(mltcuda_ctx *ctx, uint8_t *dst_yuv422, int width, int height, int position,
+                         int batch, size_t dst_bstride);
 int mltcuda_colour(mltcuda_ctx *ctx, void *dst, uint8_t *dst_alpha, int format, int width,
                    int height, uint8_t r, uint8_t g, uint8_t b, uint8_t a);
 

@@ -128,6 +128,7 @@ SIGNATURES = {
     "mltcuda_affine": (C.c_int, [vp, C.POINTER(AffineDesc)]),
     "mltcuda_tractor": (C.c_int, [vp, C.POINTER(TractorDesc)]),
     "mltcuda_noise": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, sz]),
+    "mltcuda_noise_static": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, sz]),
     "mltcuda_colour": (C.c_int, [vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_uint8, C.c_uint8, C.c_uint8, C.c_uint8]),
     "mltcuda_rescale_yuv422": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int, sz, sz]),
     "mltcuda_rescale_alpha": (C.c_int, [vp, vp, C.c_int, C.c_int, vp, C.c_int, C.c_int]),

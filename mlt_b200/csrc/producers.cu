@@ -12,6 +12,7 @@
 // digits) and then steps the generator 64 times exactly like the reference.  Bit-exact.
 #include "common.cuh"
 #include "pixel_ops.cuh"
+#include <mutex>
 
 namespace {
 
@@ -445,4 +446,104 @@ extern "C" int mltcuda_mirror_flip(mltcuda_ctx *ctx, uint8_t *dst, uint8_t *dst_
         return mc_after_launch(ctx, "k_mirror_flip_plane");
     }
     return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// mltcuda_noise_static: the noise producer for callers that must not allocate (include/mltcuda.h).
+//
+// mltcuda_noise keeps its skip-ahead tables in a cudaMalloc'ed block per context.  A render thread in
+// the middle of real-time playback cannot afford that: cudaMalloc / cudaFree take a device-wide lock
+// and wait for the GPU to drain, which stalls every other worker's stream for a frame or more; and a
+// host application that has handed all device memory to its own pool (or runs inside a fixed MIG / MPS
+// memory budget) may get cudaErrorMemoryAllocation at a moment it cannot handle.  Here the tables sit
+// in a file-scope __device__ array instead: the module image carries them, every GPU that loads this
+// library holds MLTCUDA_NOISE_STATIC_BYTES of it until the process exits, and no call -- the first
+// one included -- asks CUDA or any library for memory.
+//
+// On the host, `g_noise_tab_static` is only a handle for the symbol, not a device address; the kernel
+// must be given what cudaGetSymbolAddress returns for the CURRENT device (each GPU has its own copy).
+// That lookup and the one-time fill of the tables happen in the first call on each device, under a
+// mutex, with a blocking copy on the caller's stream -- so make that first call outside any stream
+// capture and before latency matters.  Afterwards the array is read-only: calls on any number of
+// contexts of the same GPU may overlap on the GPU without racing (they only read it), nothing has to
+// be zeroed between calls, and what one call leaves in the array is exactly what the next one needs.
+// The fill itself cannot race with a kernel either: the address is handed out only after the copy
+// has completed.  (A variant whose kernels WROTE to shared static scratch would have to serialise.)
+namespace {
+
+constexpr int NOISE_STATIC_MAX_DEVICES = 64;
+static __device__ __align__(256) uint32_t g_noise_tab_static[2 * TAB_PER_GEN];
+static_assert(sizeof(g_noise_tab_static) == MLTCUDA_NOISE_STATIC_BYTES, "header and table size disagree");
+
+std::mutex g_noise_static_mu;
+const uint32_t *g_noise_static_ptr[NOISE_STATIC_MAX_DEVICES]; // device address of the array, per GPU; null = not set up
+
+// powers of a modulo m in three digit levels (12 + 12 + 8 bits of the exponent), as k_noise's mwc_pow expects
+void noise_static_fill(uint32_t *t, uint64_t a, uint64_t m)
+{
+    const int level_len[3] = {4096, 4096, 256};
+    uint64_t base = a;
+    for (int level = 0; level < 3; level++) {
+        uint64_t v = 1;
+        for (int i = 0; i < level_len[level]; i++)
+            *t++ = (uint32_t) v, v = v * base % m;
+        base = v; // base^len: the next level's unit
+    }
+}
+
+// Device address of the static tables on ctx's GPU (which mc_use has made current); fills them on first use.
+int noise_static_table(mltcuda_ctx *ctx, const uint32_t **out)
+{
+    if (ctx->device < 0 || ctx->device >= NOISE_STATIC_MAX_DEVICES) {
+        mltcuda_set_error("mltcuda_noise_static: device %d beyond the %d this entry point tracks", ctx->device, NOISE_STATIC_MAX_DEVICES);
+        return MLTCUDA_E_UNSUPPORTED;
+    }
+    std::lock_guard<std::mutex> lock(g_noise_static_mu);
+    if (!g_noise_static_ptr[ctx->device]) {
+        uint32_t *dev = nullptr;
+        MC_CHECK(cudaGetSymbolAddress((void **) &dev, g_noise_tab_static));
+        static uint32_t host[2 * TAB_PER_GEN]; // guarded by the mutex; same contents for every GPU
+        noise_static_fill(host, MWC_A, MOD_A);
+        noise_static_fill(host + TAB_PER_GEN, MWC_B, MOD_B);
+        MC_CHECK(cudaMemcpyAsync(dev, host, sizeof(host), cudaMemcpyHostToDevice, ctx->stream));
+        MC_CHECK(cudaStreamSynchronize(ctx->stream)); // complete before any other context's stream can see the pointer
+        g_noise_static_ptr[ctx->device] = dev;
+    }
+    *out = g_noise_static_ptr[ctx->device];
+    return 0;
+}
+
+} // namespace
+
+extern "C" int mltcuda_noise_static(mltcuda_ctx *ctx, uint8_t *dst, int width, int height, int position, int batch,
+                                    size_t dst_bstride)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!dst || width < 0 || height < 0, "bad argument");
+    MC_BADARG(((uintptr_t) dst & 15) || (dst_bstride & 15), "noise destination must be 16-byte aligned");
+    const long long npx = (long long) width * height;
+    if (npx == 0)
+        return 0;
+    if (batch <= 0)
+        batch = 1;
+    if (npx > MLTCUDA_NOISE_STATIC_MAX_PIXELS || batch > MLTCUDA_NOISE_STATIC_MAX_BATCH) {
+        mltcuda_set_error("mltcuda_noise_static: %lld pixels x %d frames is beyond what the static tables reach "
+                          "(at most %lld pixels per frame, %d frames per call)",
+                          npx, batch, (long long) MLTCUDA_NOISE_STATIC_MAX_PIXELS, MLTCUDA_NOISE_STATIC_MAX_BATCH);
+        return MLTCUDA_E_BADARG;
+    }
+    MC_BADARG(batch > 1 && dst_bstride < (size_t) npx * 2, "batch > 1 needs dst_bstride >= width*height*2");
+    const uint32_t *tab = nullptr;
+    if (int e = noise_static_table(ctx, &tab))
+        return e;
+    // seed of the y generator for this timeline position and its state after two steps (producer_noise.c:37-51)
+    const uint32_t p = (uint32_t) position;
+    const uint32_t y0 = 362436069u - p + (p << 16);
+    uint32_t y2 = y0;
+    for (int k = 0; k < 2; k++)
+        y2 = MWC_B * (y2 & 65535) + (y2 >> 16);
+    dim3 grd(mc_blocks((npx + NOISE_PPT - 1) / NOISE_PPT, NOISE_THREADS), 1, batch);
+    k_noise<<<grd, NOISE_THREADS, 0, ctx->stream>>>(dst, (unsigned) npx, y2, y0, tab, dst_bstride, position, ~0ull / MOD_B);
+    return mc_after_launch(ctx, "k_noise");
 }
