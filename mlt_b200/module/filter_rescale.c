@@ -59,6 +59,14 @@ static mlt_frame wrap_process(mlt_filter filter, mlt_frame frame, mlt_get_image 
 
 /* ---- rescale ------------------------------------------------------------------------------------- */
 
+/* Has somebody replaced the scaler function ("method") core's filter_rescale_init installed
+ * (src/modules/core/filter_rescale.c:303-304) since cuda_rescale_install() looked? */
+#define CUDA_CORE_SCALER "_cuda_core_method"
+static int foreign_scaler(mlt_properties fp)
+{
+    return mlt_properties_get_data(fp, "method", NULL) != mlt_properties_get_data(fp, CUDA_CORE_SCALER, NULL);
+}
+
 static int rescale_get_image(mlt_frame frame, uint8_t **image, mlt_image_format *format, int *width, int *height, int writable)
 {
     mlt_properties p = MLT_FRAME_PROPERTIES(frame);
@@ -66,9 +74,25 @@ static int rescale_get_image(mlt_frame frame, uint8_t **image, mlt_image_format 
     const int pushed = mlt_frame_pop_service_int(frame);
     if (!is_cuda_request(frame, *format))
         return mlt_frame_get_image(frame, image, format, width, height, writable); /* the stock rescale */
+    mlt_properties fp = MLT_FILTER_PROPERTIES(filter);
+    if (foreign_scaler(fp)) {
+        /* Not core `rescale` any more: swscale and gtkrescale build themselves on it and then swap the "method"
+         * function for their own (avformat/filter_swscale.c:391-402, gdk/filter_rescale.c:140-151), and the
+         * loader prefers them (loader.ini: rescaler=movit.resample,swscale,gtkrescale,rescale).  K6 is core's
+         * nearest-neighbour scaler only, so their interpolation must stay theirs: run the stock stack for a host
+         * picture in the format the pulling service works in; whoever asked for residency uploads the result. */
+        mlt_image_format host = (mlt_image_format) mlt_properties_get_int(p, CUDA_WORK_FORMAT);
+        if (!cuda_format_supported(host))
+            host = mlt_image_yuv422;
+        const int requested = mlt_properties_get_int(p, CUDA_REQUESTED);
+        mlt_properties_set_int(p, CUDA_REQUESTED, 0);
+        const int rc = mlt_frame_get_image(frame, image, &host, width, height, writable);
+        mlt_properties_set_int(p, CUDA_REQUESTED, requested);
+        *format = host;
+        return rc;
+    }
     discard_stock_entries(frame, pushed);
 
-    mlt_properties fp = MLT_FILTER_PROPERTIES(filter);
     if (*width == 0 || *height == 0) {
         mlt_profile profile = mlt_service_profile(MLT_FILTER_SERVICE(filter));
         *width = profile->width, *height = profile->height;
@@ -264,6 +288,10 @@ static void install(mlt_filter f, process_fn ours)
 
 void cuda_rescale_install(mlt_filter stock_rescale)
 {
+    /* "filter-create-done" fires inside mlt_factory_filter(profile, "rescale"): "method" is still core's filter_scale */
+    if (stock_rescale && stock_rescale->process != rescale_process)
+        mlt_properties_set_data(MLT_FILTER_PROPERTIES(stock_rescale), CUDA_CORE_SCALER,
+                                mlt_properties_get_data(MLT_FILTER_PROPERTIES(stock_rescale), "method", NULL), 0, NULL, NULL);
     install(stock_rescale, rescale_process);
 }
 

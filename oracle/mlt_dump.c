@@ -25,6 +25,42 @@ static unsigned long long fnv1a(const unsigned char *p, size_t n)
     return h;
 }
 
+/* MLT_DUMP_FOREIGN_RESCALER=1: stand-in for swscale / gtkrescale, which this build lacks.  Like them
+ * (src/modules/avformat/filter_swscale.c:391-402, src/modules/gdk/filter_rescale.c:140-151) it is a filter that
+ * creates core `rescale` by name and then swaps the scaler function ("method") for its own; registered as
+ * "gtkrescale", which loader.ini prefers over "rescale".  The scaler is deliberately unlike core's: it samples
+ * whole units (a yuv422 pair, an rgb / rgba pixel) at the unit centres and flips one bit of each unit's first
+ * byte, so a picture that went through core's scaler -- or the device copy of it -- instead cannot match. */
+static int toy_scale(mlt_frame frame, uint8_t **image, mlt_image_format *format, int iw, int ih, int ow, int oh)
+{
+    const int unit = *format == mlt_image_rgb ? 3 : 4, ppu = *format == mlt_image_yuv422 ? 2 : 1;
+    if (*format != mlt_image_yuv422 && *format != mlt_image_rgb && *format != mlt_image_rgba)
+        return 1;
+    const int iu = iw / ppu, ou = ow / ppu;
+    const int size = mlt_image_format_size(*format, ow, oh + 1, NULL);
+    uint8_t *out = mlt_pool_alloc(size);
+    memset(out, 0, size);
+    for (int y = 0; y < oh; y++) {
+        const uint8_t *in_row = *image + (size_t) ((2 * y + 1) * ih / (2 * oh)) * iw * unit / ppu;
+        uint8_t *o = out + (size_t) y * ow * unit / ppu;
+        for (int x = 0; x < ou; x++, o += unit) {
+            memcpy(o, in_row + (size_t) ((2 * x + 1) * iu / (2 * ou)) * unit, unit);
+            o[0] ^= 0x20;
+        }
+    }
+    mlt_frame_set_image(frame, out, size, mlt_pool_release);
+    *image = out;
+    return 0;
+}
+
+static void *toy_rescaler_init(mlt_profile profile, mlt_service_type type, const char *id, const void *arg)
+{
+    mlt_filter filter = mlt_factory_filter(profile, "rescale", arg);
+    if (filter)
+        mlt_properties_set_data(MLT_FILTER_PROPERTIES(filter), "method", toy_scale, 0, NULL, NULL);
+    return filter;
+}
+
 int main(int argc, char **argv)
 {
     if (argc < 7 || strcmp(argv[5], "--")) {
@@ -33,6 +69,8 @@ int main(int argc, char **argv)
     }
     const char *rescale = getenv("MLT_DUMP_RESCALE") ? getenv("MLT_DUMP_RESCALE") : "bilinear";
     mlt_factory_init(NULL);
+    if (getenv("MLT_DUMP_FOREIGN_RESCALER"))
+        mlt_repository_register(mlt_factory_repository(), mlt_service_filter_type, "gtkrescale", toy_rescaler_init);
     mlt_profile profile = mlt_profile_init(argv[1]);
     if (!profile) {
         fprintf(stderr, "no profile %s\n", argv[1]);

@@ -460,6 +460,27 @@ def test_affine_properties_match_stock(tmp_path, name, props):
 
 
 @pytest.mark.gpu
+def test_foreign_rescaler_keeps_its_own_interpolation(tmp_path):
+    """swscale / gtkrescale are core `rescale` with the scaler function swapped, and the loader prefers them.  The
+    device nearest-neighbour scaler (K6) must not answer for them: mlt_dump's stand-in (MLT_DUMP_FOREIGN_RESCALER,
+    a scaler no other code path can imitate) has to produce the same picture with and without the module, under a
+    yuv422 composite and under an rgba affine."""
+    ex = {"MLT_DUMP_FOREIGN_RESCALER": "1"}
+    comp = A + ["-track", "noise:", "out=249", "meta.media.width=1920", "meta.media.height=1080", "-transition", "composite",
+                "a_track=0", "b_track=1", "geometry=30%/30%:30%x30%:80%", "distort=1"]
+    plain, _ = dump(tmp_path, "plain", False, "atsc_1080p_25", "yuv422", [10], comp)
+    ref, _ = dump(tmp_path, "ref", False, "atsc_1080p_25", "yuv422", [10], comp, extra=ex)
+    got, err = dump(tmp_path, "cuda", True, "atsc_1080p_25", "yuv422", [10], comp, extra=ex)
+    assert not np.array_equal(plain[10][0], ref[10][0]), "the stand-in scaler was not picked up by the loader"
+    assert np.array_equal(ref[10][0], got[10][0]), f"{(ref[10][0] != got[10][0]).sum()} bytes differ"
+    aff = A + AFFINE_B + ["-transition", "affine", "rect=20%/10%:40%x40%:80%", "b_scaled=1", "a_track=0", "b_track=1"]
+    ref, _ = dump(tmp_path, "ref", False, "atsc_1080p_25", "rgba", [30], aff, extra=ex)
+    got, _ = dump(tmp_path, "cuda", True, "atsc_1080p_25", "rgba", [30], aff, extra=ex)
+    d = np.abs(ref[30][0].astype(int) - got[30][0].astype(int))
+    assert d.max() <= 1 and (d > 0).mean() < 1e-4, f"max {d.max()}, {(d > 0).sum()} differ"
+
+
+@pytest.mark.gpu
 def test_cuda_null_consumer_takes_device_frames(tmp_path):
     """-consumer cuda.null asks for mlt_image_private; frames stay in HBM (no download), the
     deferred list still runs once per frame."""
