@@ -138,6 +138,31 @@ __attribute__((constructor)) static void cuda_stats_init(void)
     }
 }
 
+static void *g_get_image[8];
+static int g_get_image_n;
+static pthread_mutex_t g_get_image_mu = PTHREAD_MUTEX_INITIALIZER;
+
+void cuda_register_get_image(mlt_get_image fn)
+{
+    pthread_mutex_lock(&g_get_image_mu);
+    int known = 0;
+    for (int i = 0; i < g_get_image_n; i++)
+        known |= g_get_image[i] == (void *) fn;
+    if (!known && g_get_image_n < (int) (sizeof(g_get_image) / sizeof(g_get_image[0])))
+        g_get_image[g_get_image_n++] = (void *) fn;
+    pthread_mutex_unlock(&g_get_image_mu);
+}
+
+int cuda_is_module_get_image(void *fn)
+{
+    pthread_mutex_lock(&g_get_image_mu);
+    int known = 0;
+    for (int i = 0; fn && i < g_get_image_n; i++)
+        known |= g_get_image[i] == fn;
+    pthread_mutex_unlock(&g_get_image_mu);
+    return known;
+}
+
 int cuda_request_resident(mlt_frame frame, mlt_image_format requested)
 {
     mlt_properties p = MLT_FRAME_PROPERTIES(frame);
@@ -709,12 +734,15 @@ static int convert_image_impl(mlt_frame frame, uint8_t **image, mlt_image_format
         return 1; /* another module's request */
     if (ci && resident)
         return 0; /* stays in HBM; the asking service converts on the device if it must */
-    /* Device-consumer hand-off (consumer_null.c): the consumer marked the frame, so the host format it
-     * nominally asks for (mlt_image_private cannot be named in "mlt_image_format": it sorts after
-     * mlt_image_invalid, mlt_types.h:52-53) is answered with the resident picture -- the deferred list
-     * runs here, in the worker thread, an event is recorded for the consumer, nothing is copied. */
-    if (ci && mlt_properties_get_int(p, "consumer." CUDA_CONSUMER) > 0 && mlt_properties_get_int(p, CUDA_REQUESTED) <= 0)
+    /* Device-consumer hand-off (consumer_null.c): the consumer marked THIS frame for its own, next request, so
+     * the host format it nominally asks for (mlt_image_private cannot be named in "mlt_image_format": it sorts
+     * after mlt_image_invalid, mlt_types.h:52-53) is answered with the resident picture -- the deferred list
+     * runs here, in the worker thread, an event is recorded for the consumer, nothing is copied.  The mark is
+     * spent here: whoever asks this frame for a host format afterwards gets pixels. */
+    if (ci && mlt_properties_get_int(p, CUDA_HANDOFF) > 0 && mlt_properties_get_int(p, CUDA_REQUESTED) <= 0) {
+        mlt_properties_set_int(p, CUDA_HANDOFF, 0);
         return cuda_image_mark_ready(ci);
+    }
 
     if (!ci) { /* host image */
         /* host -> host is the imageconvert filter's job, in the filter's place in the chain (the

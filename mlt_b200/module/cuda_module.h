@@ -28,7 +28,13 @@
 #define CUDA_IMAGE_TAG "mlt_image_private"
 #define CUDA_IMAGE_TAG_VALUE "cuda"
 #define CUDA_REQUESTED "_cuda_requested"
-#define CUDA_CONSUMER "_cuda_consumer" /* the consumer itself takes device frames (consumer_null.c): flush at hand-off, no download */
+#define CUDA_CONSUMER "_cuda_consumer" /* set by a device consumer (consumer_null.c) on the frames it handed off: their image is a cuda_image */
+/* One-shot, set by a device consumer on the ONE frame whose next host-format request provably comes from the
+ * consumer itself (consumer_null.c: consumer_is_sole_requester): the converter answers that request with the
+ * resident picture instead of a download, and clears the mark.  Deliberately without the "consumer." prefix:
+ * mlt_tractor (mlt_tractor.c:366) and mlt_transition (mlt_transition.c:378) copy "consumer." properties to track
+ * and B frames, where a stock CPU service asking for yuv422 must get pixels, not a handle. */
+#define CUDA_HANDOFF "_cuda_handoff"
 #define CUDA_WORK_FORMAT "_cuda_work_format" /* format the pulling service will work in (hint for device producers) */
 
 /* Deferred op list of one image (precedent: the per-frame effect chain of
@@ -150,6 +156,10 @@ void cuda_resize_install(mlt_filter stock_resize);
 void cuda_mirror_install(mlt_filter stock_mirror); /* mirror:flip between a device producer and a CUDA transition */
 /* cuda_image.c: registers the imageconvert filter's converter on a frame (appended, like the reference) */
 void cuda_imageconvert_attach(mlt_frame frame);
+/* The get_image callbacks this module's transitions push (registered by their constructors): lets a device consumer
+ * check that the service on top of a frame's image stack is one that understands the hand-off. */
+void cuda_register_get_image(mlt_get_image fn);
+int cuda_is_module_get_image(void *fn);
 /* true if a device producer may answer this request with a resident image */
 int cuda_request_resident(mlt_frame frame, mlt_image_format requested);
 

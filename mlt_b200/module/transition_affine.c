@@ -399,6 +399,7 @@ static mlt_frame affine_process(mlt_transition self, mlt_frame a_frame, mlt_fram
 
 mlt_transition cuda_transition_affine_init(mlt_profile profile, mlt_service_type type, const char *id, char *arg)
 {
+    cuda_register_get_image(affine_get_image);
     mlt_transition self = mlt_transition_new();
     if (!self)
         return NULL;

@@ -514,6 +514,7 @@ static mlt_frame composite_process(mlt_transition self, mlt_frame a_frame, mlt_f
 
 mlt_transition cuda_transition_composite_init(mlt_profile profile, mlt_service_type type, const char *id, char *arg)
 {
+    cuda_register_get_image(composite_get_image);
     mlt_transition self = mlt_transition_new();
     if (!self)
         return NULL;

@@ -296,6 +296,7 @@ static mlt_frame luma_process(mlt_transition self, mlt_frame a_frame, mlt_frame 
 
 mlt_transition cuda_transition_luma_init(mlt_profile profile, mlt_service_type type, const char *id, char *lumafile)
 {
+    cuda_register_get_image(luma_get_image);
     mlt_transition self = mlt_transition_new();
     if (!self)
         return NULL;

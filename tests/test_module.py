@@ -501,3 +501,28 @@ def test_cuda_null_consumer_takes_device_frames(tmp_path):
     assert "download + sync" not in stats and "upload" not in stats, stats
     # (frames melt pulls again while it stops are dropped before their hand-off)
     assert n <= stats.get("fused pass (k_tractor launches)") <= frames, stats
+
+
+@pytest.mark.gpu
+def test_cuda_null_hands_off_only_to_itself(tmp_path):
+    """A stock CPU filter planted above the last CUDA transition (greyscale on track 0) asks the rendered frame for
+    yuv422 before the consumer does.  It must get pixels: cuda.null may take the device handle only when its own
+    request is provably the first host-format one (consumer_null.c: consumer_is_sole_requester), so here every
+    frame is downloaded for the filter and nothing is handed off."""
+    e = mltenv.env(str(tmp_path), cuda=True)
+    e["MLT_CUDA_STATS"] = "1"
+    n = 12
+    args = ["noise:", f"out={n - 1}", "-track", "noise:", f"out={n - 1}", "-transition", "composite", "a_track=0", "b_track=1",
+            "geometry=25%/25%:50%x50%:50%", "-filter", "greyscale", "track=0"]
+    r = subprocess.run([mltenv.MELT, "-profile", "atsc_1080p_25"] + args + ["-consumer", "cuda.null", "real_time=-2",
+                                                                            "terminate_on_pause=1", "-silent"],
+                       env=e, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    stats = {}
+    for ln in r.stderr.splitlines():
+        if ln.startswith("[cuda stats]") and "calls" in ln:
+            name, rest = ln[len("[cuda stats] "):].split("calls")
+            stats[name.strip()] = int(rest.split()[0])
+    frames = stats.get("composite get_image (incl. inputs)")
+    assert frames and frames >= n, (stats, r.stderr[-1500:])
+    assert stats.get("download + sync") == frames, stats
