@@ -111,6 +111,12 @@ void mltcuda_graph_destroy(mltcuda_graph *g);
  * Lets the host write an opaque alpha plane itself instead of copying it over PCIe. */
 int mltcuda_plane_opaque_query(mltcuda_ctx *ctx, const uint8_t *plane_dev, size_t bytes);
 int mltcuda_plane_opaque_result(const mltcuda_ctx *ctx);
+/* The same query with the verdict in a word the CALLER owns, for contexts that more than one thread submits to
+ * (_query/_result share one slot per context).  `translucent_pinned` must be pinned host memory
+ * (mltcuda_host_alloc, mltcuda_host_pool_alloc or mltcuda_host_register); it is cleared by this call and, after the
+ * next mltcuda_ctx_sync / event wait behind it, holds 0 if every byte of the plane is 0xff and 1 otherwise.  The
+ * slot must stay allocated, and must not be reused for another query, until then. */
+int mltcuda_plane_opaque_query_into(mltcuda_ctx *ctx, const uint8_t *plane_dev, size_t bytes, int *translucent_pinned);
 
 /* CUDA-event timing on the context stream (used by bench.py; torch events do not see it). */
 typedef struct mltcuda_event mltcuda_event;

@@ -108,6 +108,7 @@ SIGNATURES = {
     "mltcuda_graph_destroy": (None, [vp]),
     "mltcuda_plane_opaque_query": (C.c_int, [vp, vp, sz]),
     "mltcuda_plane_opaque_result": (C.c_int, [vp]),
+    "mltcuda_plane_opaque_query_into": (C.c_int, [vp, vp, sz, vp]),
     "mltcuda_event_create": (vp, []),
     "mltcuda_event_destroy": (None, [vp]),
     "mltcuda_event_record": (C.c_int, [vp, vp]),

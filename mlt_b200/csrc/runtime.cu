@@ -340,6 +340,32 @@ int mltcuda_plane_opaque_result(const mltcuda_ctx *ctx)
     return ctx && ctx->opaque_host ? *ctx->opaque_host == 0 : 0;
 }
 
+// The same question with the verdict in memory the caller owns.  The per-context slot above is shared by every
+// query on the context: when two threads download images that live on one context, each can read the other's
+// verdict (or have its device flag cleared under it) and an alpha plane with real transparency is then replaced
+// by 0xff.  Here the kernel raises the caller's pinned word directly (pinned host memory is device-addressable
+// under unified addressing), so a query owns nothing but its own slot: no device flag, no memset, no copy.
+int mltcuda_plane_opaque_query_into(mltcuda_ctx *ctx, const uint8_t *plane, size_t bytes, int *translucent_pinned)
+{
+    if (int e = mc_use(ctx))
+        return e;
+    MC_BADARG(!plane || ((uintptr_t) plane & 15), "plane must be a 16-byte aligned device pointer");
+    MC_BADARG(!translucent_pinned, "null verdict slot");
+    int *dev_alias = nullptr;
+    cudaError_t e = cudaHostGetDevicePointer((void **) &dev_alias, translucent_pinned, 0);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        mltcuda_set_error("mltcuda_plane_opaque_query_into: the verdict slot must be pinned host memory "
+                          "(mltcuda_host_alloc / mltcuda_host_pool_alloc / mltcuda_host_register): %s", cudaGetErrorString(e));
+        return (int) e;
+    }
+    *translucent_pinned = 0; // the caller's slot: nothing on the GPU touches it before the kernel below
+    const size_t n16 = bytes / 16;
+    k_plane_not_ff<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>((const uint4 *) plane, n16, plane + n16 * 16, (int) (bytes - n16 * 16),
+                                                             dev_alias);
+    return mc_after_launch(ctx, "k_plane_not_ff");
+}
+
 // ---- CUDA graphs: a launch-bound sequence (hundreds of per-frame launches on one or several contexts) recorded
 // once and replayed with one call, so the host's launch rate is out of the picture.
 struct mltcuda_graph

@@ -537,16 +537,20 @@ int cuda_download_to_frame(mlt_frame frame, cuda_image ci, uint8_t **image, mlt_
         alpha_dma = e && *e && *e != '0';
     }
     int rc = mltcuda_download(ci->ctx, host, ci->data, bytes);
-    const int query = !rc && abytes && !alpha_dma && !((uintptr_t) ci->alpha & 15);
+    /* The verdict lands in a pinned word of this call's own: ci->ctx may be another thread's context (an adopted
+     * idle one, an image cloned onto its producer's context, a consumer asking again), and two downloads on one
+     * context must not read each other's answer. */
+    int *translucent = !rc && abytes && !alpha_dma && !((uintptr_t) ci->alpha & 15) ? mltcuda_host_pool_alloc(sizeof(int)) : NULL;
+    const int query = translucent != NULL;
     if (query)
-        rc = mltcuda_plane_opaque_query(ci->ctx, ci->alpha, abytes);
+        rc = mltcuda_plane_opaque_query_into(ci->ctx, ci->alpha, abytes, translucent);
     else if (!rc && abytes)
         rc = mltcuda_download(ci->ctx, ahost, ci->alpha, abytes);
     if (!rc)
         rc = mltcuda_ctx_sync(ci->ctx);
     size_t moved = bytes + abytes;
     if (!rc && query) {
-        if (mltcuda_plane_opaque_result(ci->ctx)) {
+        if (!*translucent) {
             memset(ahost, 0xff, abytes);
             moved = bytes;
         } else {
@@ -555,6 +559,8 @@ int cuda_download_to_frame(mlt_frame frame, cuda_image ci, uint8_t **image, mlt_
                 rc = mltcuda_ctx_sync(ci->ctx);
         }
     }
+    if (translucent)
+        mltcuda_host_pool_release(translucent);
     CUDA_STAT_END(CS_DOWNLOAD, st0);
     if (cuda_stats_on)
         cuda_stat_bytes(CS_DOWNLOAD, moved);

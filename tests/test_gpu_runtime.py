@@ -78,6 +78,40 @@ def test_plane_opaque_query(ctx, nbytes):
         assert lib.mltcuda_plane_opaque_result(ctx.h) == 0, pos
 
 
+def test_plane_opaque_query_into_keeps_verdicts_apart(ctx):
+    """Two queries queued on ONE context before a single sync -- what two threads downloading images of the same
+    context do -- each with a pinned word of its own: neither sees the other's verdict, in either order."""
+    lib = ctx.lib
+    n = 1920 * 1080
+    opaque = ctx.put(np.full(n, 0xff, np.uint8))
+    holed = np.full(n, 0xff, np.uint8)
+    holed[n - 3] = 0x7f
+    holed = ctx.put(holed)
+    slots = [lib.mltcuda_host_pool_alloc(4) for _ in range(4)]
+    words = [C.cast(s, C.POINTER(C.c_int)) for s in slots]
+    try:
+        for w in words:
+            w[0] = 77  # stale contents must not matter
+        for s, plane in zip(slots, (opaque, holed, holed, opaque)):
+            abi.check(lib.mltcuda_plane_opaque_query_into(ctx.h, plane.ptr, n, s))
+        ctx.sync()
+        assert [w[0] for w in words] == [0, 1, 1, 0]
+        # ragged sizes and the tail bytes, as in test_plane_opaque_query
+        for nbytes in (1, 15, 17, 3840 * 2160 + 5):
+            plane = np.full(nbytes, 0xff, np.uint8)
+            abi.check(lib.mltcuda_plane_opaque_query_into(ctx.h, ctx.put(plane).ptr, nbytes, slots[0]))
+            plane[nbytes - 1] = 0
+            abi.check(lib.mltcuda_plane_opaque_query_into(ctx.h, ctx.put(plane).ptr, nbytes, slots[1]))
+            ctx.sync()
+            assert (words[0][0], words[1][0]) == (0, 1), nbytes
+        pageable = (C.c_int * 1)()
+        assert lib.mltcuda_plane_opaque_query_into(ctx.h, opaque.ptr, n, C.addressof(pageable)) != 0
+        assert b"pinned" in lib.mltcuda_last_error()
+    finally:
+        for s in slots:
+            lib.mltcuda_host_pool_release(s)
+
+
 def test_graph_capture_replays_launches_on_two_contexts():
     """mltcuda_graph_*: a sequence recorded on one context, with a second context forked in and joined back through
     events, replays with one call and produces what the plain launches produce."""
