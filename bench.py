@@ -642,6 +642,13 @@ def run_ours(args, dist):
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_max / args.steps, 4),
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
                 "config": dict(CONFIG),
+                # which number answers which question (advisor, round 2): `value` has no host path in it
+                "regions": {"value": "DEVICE CEILING: kernels only, inputs resident in HBM, no upload, download or MLT host code -- "
+                                     "explains the roofline; not comparable with --impl reference",
+                            "e2e": "HEADLINE, like for like with --impl reference and cpu_baseline: the same melt command line and "
+                                   "host consumer, producers included, every frame delivered to host memory",
+                            "e2e_resident": "same melt run with a device consumer (no download)",
+                            "e2e_abi": "C-ABI loop with real uploads and downloads, no MLT host"},
                 "arm": {"timed_region": "per frame 3 k_noise (tracks 0, 1, 3) + k_mirror_flip (track 1) + 1 k_tractor = the melt graph's "
                                         "device work; colour track resident (constant)",
                         "launches_per_frame": round(total_launches / (dist.world * FRAMES_PER_STEP * args.steps), 3),

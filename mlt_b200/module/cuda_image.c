@@ -246,6 +246,13 @@ void cuda_image_close(cuda_image ci)
         mltcuda_free(ci->ctx, ci->alpha);
     if (ci->ready)
         mltcuda_event_destroy(ci->ready);
+    for (cuda_retired *r = ci->retired; r;) { /* every list that read them has launched and released its reference */
+        cuda_retired *next = r->next;
+        mltcuda_free(r->ctx, r->data);
+        mltcuda_free(r->ctx, r->alpha);
+        free(r);
+        r = next;
+    }
     ci->magic = 0;
     free(ci);
 }
@@ -306,6 +313,9 @@ static void pending_release(cuda_image a, cuda_pending *p, int launched)
         if (p->keep[i]) {
             if (launched && p->keep[i]->ctx != a->ctx)
                 mltcuda_ctx_wait_ctx(p->keep[i]->ctx, a->ctx);
+            for (cuda_retired *r = launched ? p->keep[i]->retired : NULL; r; r = r->next)
+                if (r->ctx != a->ctx) /* the kernel may have read buffers the image has since moved out of */
+                    mltcuda_ctx_wait_ctx(r->ctx, a->ctx);
             cuda_image_close(p->keep[i]);
         }
     free(p);
@@ -336,8 +346,17 @@ int cuda_image_localize(cuda_image b, mltcuda_ctx *ctx)
         return 1;
     }
     mltcuda_ctx_wait_ctx(b->ctx, ctx); /* the old buffers are freed on b's stream: after the copy */
-    mltcuda_free(b->ctx, b->data);
-    mltcuda_free(b->ctx, b->alpha);
+    cuda_retired *r = __atomic_load_n(&b->refs, __ATOMIC_ACQUIRE) > 1 ? calloc(1, sizeof(*r)) : NULL;
+    if (r) {
+        /* Somebody besides the frame holds the handle: a deferred list that has not launched yet, and that
+         * recorded b->data / b->alpha when its op was appended.  Those addresses must stay good until it has run,
+         * so the old buffers retire with the handle instead of being freed here. */
+        r->ctx = b->ctx, r->data = b->data, r->alpha = b->alpha, r->next = b->retired;
+        b->retired = r;
+    } else {
+        mltcuda_free(b->ctx, b->data);
+        mltcuda_free(b->ctx, b->alpha);
+    }
     b->data = data, b->alpha = alpha, b->ctx = ctx;
     return 0;
 }

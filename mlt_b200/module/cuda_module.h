@@ -52,6 +52,15 @@ typedef struct cuda_pending_s
     cuda_image keep[MLTCUDA_TRACTOR_MAX_OPS]; /* B images the ops read: retained until the launch */
 } cuda_pending;
 
+/* Buffers an image had before it moved to another GPU while a deferred list still held their addresses
+ * (cuda_image_localize): kept until the last reference to the handle goes. */
+typedef struct cuda_retired_s
+{
+    mltcuda_ctx *ctx;
+    void *data, *alpha;
+    struct cuda_retired_s *next;
+} cuda_retired;
+
 struct cuda_image_s
 {
     uint32_t magic;
@@ -63,6 +72,7 @@ struct cuda_image_s
     uint8_t *alpha;        /* device, 1 B/px, or NULL (same remark) */
     cuda_pending *pending; /* NULL = the buffers hold the image */
     mltcuda_event *ready;  /* recorded behind the last launch when the image is handed to a device consumer */
+    cuda_retired *retired; /* earlier buffers that pending lists of other images may still read */
 };
 
 /* --- runtime (cuda_image.c) -------------------------------------------------------------- */
