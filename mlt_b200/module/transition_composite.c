@@ -377,7 +377,14 @@ static int composite_get_image_impl(mlt_frame a_frame, uint8_t **image, mlt_imag
         goto done;
     if (!b)
         b = pull_b(self, b_frame, &width_b, &height_b, &g);
-    if (!b || b == a)
+    if (!b) {
+        /* The reference also leaves A untouched when B yields no image (:1063).  Here "no image" includes a device
+         * allocation or upload that failed, which should not vanish silently. */
+        mlt_log_warning(service, "[cuda] composite: B image unavailable at position %d, layer skipped (%s)\n",
+                        (int) mlt_frame_get_position(a_frame), mltcuda_last_error());
+        goto done;
+    }
+    if (b == a)
         goto done;
 
     const int progressive = mlt_properties_get_int(a_props, "consumer.progressive")
