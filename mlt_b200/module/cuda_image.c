@@ -694,9 +694,10 @@ static int frame_image_to_format(mlt_frame frame, cuda_image *pci, mlt_image_for
     }
     if (shared) {
         cuda_image c2 = cuda_image_convert(ci, format);
-        if (c2 && ci->alpha == NULL && c2->alpha && format != mlt_image_yuv422 && ci->format != mlt_image_rgba
-            && ci->format != mlt_image_rgba64) {
-            /* cuda_image_convert MOVED a carried-along alpha plane out of the shared source: give it a copy back */
+        if (c2 && ci->alpha == NULL && c2->alpha && ci->format != mlt_image_rgba && ci->format != mlt_image_rgba64) {
+            /* cuda_image_convert MOVED a carried-along alpha plane out of the shared source (the only way a source
+             * without alpha in its pixels yields a plane, whatever the target -- rgb / yuv420p -> yuv422 included):
+             * give it a copy back */
             ci->alpha = mltcuda_malloc(ci->ctx, (size_t) ci->width * ci->height);
             if (ci->alpha)
                 mltcuda_copy(ci->ctx, ci->alpha, c2->alpha, (size_t) ci->width * ci->height);
